@@ -1,0 +1,665 @@
+// api.cu -- the C ABI of libnexus_flat.so (see include/nexus_flat.h): index handle, add / convert /
+// shard upload, search dispatch (K2 stream | K1 tcgen05 | KX exact), merge, pool+normalise.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "params.cuh"
+
+namespace nxf {
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  set_error("CUDA error %d (%s) at %s:%d in `%s`", static_cast<int>(e), cudaGetErrorString(e), file, line, what);
+  if (e == cudaErrorMemoryAllocation) return NXF_ENOMEM;
+  if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver || e == cudaErrorInvalidDevice) return NXF_ENODEVICE;
+  return NXF_ECUDA;
+}
+
+}  // namespace nxf
+
+using namespace nxf;
+
+// ------------------------------------------------------------------------------------------
+// the handle
+// ------------------------------------------------------------------------------------------
+struct nxf_index {
+  int dim = 0, metric = 0, store_dtype = 0, device = 0;
+  int64_t ld = 0;          // stored row stride in elements (dim rounded up to 64, zero padded)
+  int64_t n = 0, capacity = 0;
+  void* data = nullptr;    // [capacity, ld] of store_dtype
+  float* half_norm = nullptr;  // [capacity] 0.5*|row|^2 (L2 only)
+  int64_t id_offset = 0;
+  int sm_count = 0;
+  int cc_major = 0;
+  // scratch arena (grown on demand, reused across searches)
+  unsigned char* scratch = nullptr;
+  size_t scratch_bytes = 0;
+  // pinned staging for host <-> device traffic
+  unsigned char* pinned = nullptr;
+  size_t pinned_bytes = 0;
+  nxf_stats stats{};
+  std::mutex mu;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    ok = (cudaSetDevice(dev) == cudaSuccess);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+int check_dtype(int dt, const char* what) {
+  if (dt != NXF_F32 && dt != NXF_F16 && dt != NXF_BF16) {
+    set_error("%s: unknown dtype %d (NXF_F32=0, NXF_F16=1, NXF_BF16=2)", what, dt);
+    return NXF_EINVAL;
+  }
+  return NXF_OK;
+}
+
+int ensure_scratch(nxf_index* idx, size_t bytes) {
+  if (bytes <= idx->scratch_bytes) return NXF_OK;
+  if (idx->scratch) { cudaFree(idx->scratch); idx->scratch = nullptr; idx->scratch_bytes = 0; }
+  const size_t want = (bytes + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
+  NXF_CUDA(cudaMalloc(reinterpret_cast<void**>(&idx->scratch), want));
+  idx->scratch_bytes = want;
+  idx->stats.scratch_bytes = static_cast<int64_t>(want);
+  return NXF_OK;
+}
+
+int ensure_pinned(nxf_index* idx, size_t bytes) {
+  if (bytes <= idx->pinned_bytes) return NXF_OK;
+  if (idx->pinned) { cudaFreeHost(idx->pinned); idx->pinned = nullptr; idx->pinned_bytes = 0; }
+  NXF_CUDA(cudaMallocHost(reinterpret_cast<void**>(&idx->pinned), bytes));
+  idx->pinned_bytes = bytes;
+  return NXF_OK;
+}
+
+int ensure_capacity(nxf_index* idx, int64_t want, cudaStream_t stream) {
+  if (want <= idx->capacity) return NXF_OK;
+  int64_t cap = std::max<int64_t>(want, idx->capacity + idx->capacity / 2);
+  cap = round_up64(cap, 256);
+  const size_t esz = dtype_size(idx->store_dtype);
+  void* nd = nullptr;
+  // +256 rows of slack so that tile-granular TMA boxes never leave the allocation
+  NXF_CUDA(cudaMalloc(&nd, static_cast<size_t>(cap + 256) * idx->ld * esz));
+  float* nh = nullptr;
+  if (idx->metric == NXF_METRIC_L2) {
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&nh), static_cast<size_t>(cap + 256) * sizeof(float));
+    if (e != cudaSuccess) { cudaFree(nd); return cuda_fail(e, "cudaMalloc(half_norm)", __FILE__, __LINE__); }
+  }
+  if (idx->n > 0) {
+    NXF_CUDA(cudaMemcpyAsync(nd, idx->data, static_cast<size_t>(idx->n) * idx->ld * esz, cudaMemcpyDeviceToDevice, stream));
+    if (nh) NXF_CUDA(cudaMemcpyAsync(nh, idx->half_norm, static_cast<size_t>(idx->n) * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+    NXF_CUDA(cudaStreamSynchronize(stream));
+  }
+  if (idx->data) cudaFree(idx->data);
+  if (idx->half_norm) cudaFree(idx->half_norm);
+  idx->data = nd;
+  idx->half_norm = nh;
+  idx->capacity = cap;
+  idx->stats.storage_bytes = static_cast<int64_t>((cap + 256) * idx->ld * esz);
+  return NXF_OK;
+}
+
+// choose the number of corpus chunks so that (query tiles x chunks) fills `grid` CTAs evenly
+void plan_units(int num_qt, int64_t n_tiles, int grid, int* chunks_out, int64_t* tpc_out) {
+  if (n_tiles <= 0) { *chunks_out = 1; *tpc_out = 1; return; }
+  const int64_t max_chunks = std::max<int64_t>(1, std::min<int64_t>(n_tiles, 4 * static_cast<int64_t>(grid)));
+  int64_t best_c = 1;
+  double best_eff = -1.0;
+  for (int64_t c = 1; c <= max_chunks; ++c) {
+    const int64_t tpc = ceil_div64(n_tiles, c);
+    const int64_t cc = ceil_div64(n_tiles, tpc);
+    const int64_t units = cc * num_qt;
+    const int64_t waves = ceil_div64(units, grid);
+    // cost model: every wave costs tpc tile-times (+1 for per-unit flush overhead)
+    const double cost = static_cast<double>(waves) * static_cast<double>(tpc + 1);
+    const double ideal = static_cast<double>(n_tiles) * num_qt / grid;
+    const double eff = ideal / cost;
+    if (eff > best_eff + 1e-9) { best_eff = eff; best_c = cc; }
+    if (eff >= 0.985) break;
+  }
+  const int64_t tpc = ceil_div64(n_tiles, best_c);
+  *tpc_out = tpc;
+  *chunks_out = static_cast<int>(ceil_div64(n_tiles, tpc));
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int env_int(const char* name, int dflt) {
+  const char* v = std::getenv(name);
+  if (!v || !*v) return dflt;
+  return std::atoi(v);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// library
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* nxf_version(void) { return "nexus_flat 0.1.0 (sm_100a; tcgen05/TMA)"; }
+const char* nxf_last_error(void) { return g_err; }
+
+int nxf_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return cuda_fail(e, "cudaGetDeviceCount", __FILE__, __LINE__);
+  }
+  return n;
+}
+
+int nxf_create(int dim, int metric, int store_dtype, int device, nxf_index** out) {
+  NXF_REQUIRE(out != nullptr, "nxf_create: out is NULL");
+  *out = nullptr;
+  NXF_REQUIRE(dim >= 1 && dim <= 16384, "nxf_create: dim %d out of range [1, 16384]", dim);
+  NXF_REQUIRE(metric == NXF_METRIC_IP || metric == NXF_METRIC_L2, "nxf_create: unknown metric %d", metric);
+  int rc = check_dtype(store_dtype, "nxf_create(store_dtype)");
+  if (rc) return rc;
+  int ndev = nxf_device_count();
+  if (ndev < 0) return ndev;
+  if (ndev == 0) { set_error("nxf_create: no CUDA device is visible; this engine has no CPU fallback"); return NXF_ENODEVICE; }
+  NXF_REQUIRE(device >= 0 && device < ndev, "nxf_create: device %d out of range (visible devices: %d)", device, ndev);
+  cudaDeviceProp prop;
+  NXF_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("nxf_create: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
+    return NXF_ENODEVICE;
+  }
+  nxf_index* idx = new (std::nothrow) nxf_index();
+  if (!idx) { set_error("nxf_create: out of host memory"); return NXF_ENOMEM; }
+  idx->dim = dim;
+  idx->metric = metric;
+  idx->store_dtype = store_dtype;
+  idx->device = device;
+  idx->ld = round_up64(dim, 64);
+  idx->sm_count = prop.multiProcessorCount;
+  idx->cc_major = prop.major;
+  *out = idx;
+  return NXF_OK;
+}
+
+void nxf_destroy(nxf_index* idx) {
+  if (!idx) return;
+  {
+    DeviceGuard g(idx->device);
+    if (idx->data) cudaFree(idx->data);
+    if (idx->half_norm) cudaFree(idx->half_norm);
+    if (idx->scratch) cudaFree(idx->scratch);
+    if (idx->pinned) cudaFreeHost(idx->pinned);
+  }
+  delete idx;
+}
+
+int nxf_reset(nxf_index* idx) {
+  NXF_REQUIRE(idx != nullptr, "nxf_reset: NULL index");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  idx->n = 0;
+  return NXF_OK;
+}
+
+int nxf_reserve(nxf_index* idx, int64_t n_total) {
+  NXF_REQUIRE(idx != nullptr, "nxf_reserve: NULL index");
+  NXF_REQUIRE(n_total >= 0 && n_total < (int64_t(1) << 31) - 512, "nxf_reserve: %lld rows exceed the per-device limit", (long long)n_total);
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  return ensure_capacity(idx, n_total, nullptr);
+}
+
+int64_t nxf_ntotal(const nxf_index* idx) { return idx ? idx->n : -1; }
+int nxf_dim(const nxf_index* idx) { return idx ? idx->dim : -1; }
+int nxf_metric(const nxf_index* idx) { return idx ? idx->metric : -1; }
+int nxf_store_dtype(const nxf_index* idx) { return idx ? idx->store_dtype : -1; }
+int nxf_device(const nxf_index* idx) { return idx ? idx->device : -1; }
+
+int nxf_set_id_offset(nxf_index* idx, int64_t offset) {
+  NXF_REQUIRE(idx != nullptr, "nxf_set_id_offset: NULL index");
+  idx->id_offset = offset;
+  return NXF_OK;
+}
+
+int nxf_get_stats(const nxf_index* idx, nxf_stats* out) {
+  NXF_REQUIRE(idx != nullptr && out != nullptr, "nxf_get_stats: NULL argument");
+  *out = idx->stats;
+  return NXF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// add
+// ------------------------------------------------------------------------------------------
+int nxf_add(nxf_index* idx, const void* rows, int64_t n, int src_dtype, int64_t src_ld, int src_on_device, void* stream_) {
+  NXF_REQUIRE(idx != nullptr, "nxf_add: NULL index");
+  NXF_REQUIRE(n >= 0, "nxf_add: negative row count");
+  if (n == 0) return NXF_OK;
+  NXF_REQUIRE(rows != nullptr, "nxf_add: rows is NULL");
+  int rc = check_dtype(src_dtype, "nxf_add(src_dtype)");
+  if (rc) return rc;
+  if (src_ld == 0) src_ld = idx->dim;
+  NXF_REQUIRE(src_ld >= idx->dim, "nxf_add: row stride %lld smaller than dim %d", (long long)src_ld, idx->dim);
+  std::lock_guard<std::mutex> lk(idx->mu);
+  NXF_REQUIRE(idx->n + n < (int64_t(1) << 31) - 512, "nxf_add: %lld rows exceed the per-device limit (shard across devices)",
+              (long long)(idx->n + n));
+  DeviceGuard g(idx->device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  rc = ensure_capacity(idx, idx->n + n, stream);
+  if (rc) return rc;
+  const size_t esz = dtype_size(idx->store_dtype);
+  const size_t ssz = dtype_size(src_dtype);
+  unsigned char* dst = static_cast<unsigned char*>(idx->data) + static_cast<size_t>(idx->n) * idx->ld * esz;
+
+  if (src_on_device) {
+    rc = launch_convert_rows(rows, src_dtype, src_ld, dst, idx->store_dtype, idx->ld, n, idx->dim, stream);
+    if (rc) return rc;
+    idx->stats.kernel_launches++;
+  } else {
+    // host rows: double-buffered pinned staging -> async H2D -> convert/re-pitch on the device
+    const size_t row_bytes = static_cast<size_t>(src_ld) * ssz;
+    const size_t chunk_rows = std::max<size_t>(1, std::min<size_t>(static_cast<size_t>(n), (size_t(64) << 20) / row_bytes));
+    const size_t chunk_bytes = chunk_rows * row_bytes;
+    rc = ensure_pinned(idx, 2 * chunk_bytes);
+    if (rc) return rc;
+    rc = ensure_scratch(idx, 2 * chunk_bytes);
+    if (rc) return rc;
+    cudaEvent_t ev[2];
+    NXF_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+    NXF_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+    const unsigned char* src = static_cast<const unsigned char*>(rows);
+    int b = 0;
+    bool used[2] = {false, false};
+    for (int64_t r0 = 0; r0 < n; r0 += static_cast<int64_t>(chunk_rows), b ^= 1) {
+      const int64_t rn = std::min<int64_t>(static_cast<int64_t>(chunk_rows), n - r0);
+      if (used[b]) NXF_CUDA(cudaEventSynchronize(ev[b]));  // staging buffer b free again
+      std::memcpy(idx->pinned + b * chunk_bytes, src + static_cast<size_t>(r0) * row_bytes, static_cast<size_t>(rn) * row_bytes);
+      NXF_CUDA(cudaMemcpyAsync(idx->scratch + b * chunk_bytes, idx->pinned + b * chunk_bytes, static_cast<size_t>(rn) * row_bytes,
+                               cudaMemcpyHostToDevice, stream));
+      rc = launch_convert_rows(idx->scratch + b * chunk_bytes, src_dtype, src_ld, dst + static_cast<size_t>(r0) * idx->ld * esz,
+                               idx->store_dtype, idx->ld, rn, idx->dim, stream);
+      if (rc) return rc;
+      idx->stats.kernel_launches++;
+      NXF_CUDA(cudaEventRecord(ev[b], stream));
+      used[b] = true;
+    }
+    NXF_CUDA(cudaStreamSynchronize(stream));
+    cudaEventDestroy(ev[0]);
+    cudaEventDestroy(ev[1]);
+  }
+  if (idx->metric == NXF_METRIC_L2) {
+    rc = launch_half_norm(dst, idx->store_dtype, idx->ld, n, idx->dim, idx->half_norm + idx->n, stream);
+    if (rc) return rc;
+    idx->stats.kernel_launches++;
+  }
+  idx->n += n;
+  idx->stats.rows_added += n;
+  return NXF_OK;
+}
+
+int nxf_reconstruct(nxf_index* idx, int64_t first, int64_t n, float* dst, int dst_on_device, void* stream_) {
+  NXF_REQUIRE(idx != nullptr && dst != nullptr, "nxf_reconstruct: NULL argument");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  NXF_REQUIRE(first >= 0 && n >= 0 && first + n <= idx->n, "nxf_reconstruct: rows [%lld, %lld) outside [0, %lld)", (long long)first,
+              (long long)(first + n), (long long)idx->n);
+  if (n == 0) return NXF_OK;
+  DeviceGuard g(idx->device);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const size_t esz = dtype_size(idx->store_dtype);
+  const unsigned char* src = static_cast<const unsigned char*>(idx->data) + static_cast<size_t>(first) * idx->ld * esz;
+  if (dst_on_device) {
+    int rc = launch_convert_rows(src, idx->store_dtype, idx->ld, dst, NXF_F32, idx->dim, n, idx->dim, stream);
+    if (rc) return rc;
+    idx->stats.kernel_launches++;
+    return NXF_OK;
+  }
+  const int64_t chunk = std::max<int64_t>(1, (int64_t(64) << 20) / (static_cast<int64_t>(idx->dim) * 4));
+  int rc = ensure_scratch(idx, static_cast<size_t>(std::min(chunk, n)) * idx->dim * 4);
+  if (rc) return rc;
+  for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+    const int64_t rn = std::min(chunk, n - r0);
+    rc = launch_convert_rows(src + static_cast<size_t>(r0) * idx->ld * esz, idx->store_dtype, idx->ld, idx->scratch, NXF_F32, idx->dim, rn,
+                             idx->dim, stream);
+    if (rc) return rc;
+    idx->stats.kernel_launches++;
+    NXF_CUDA(cudaMemcpyAsync(dst + r0 * idx->dim, idx->scratch, static_cast<size_t>(rn) * idx->dim * 4, cudaMemcpyDeviceToHost, stream));
+    NXF_CUDA(cudaStreamSynchronize(stream));
+  }
+  return NXF_OK;
+}
+
+}  // extern "C" (search helpers below are C++)
+
+// ------------------------------------------------------------------------------------------
+// search
+// ------------------------------------------------------------------------------------------
+namespace {
+
+struct Carver {
+  unsigned char* base;
+  size_t off = 0;
+  explicit Carver(unsigned char* b) : base(b) {}
+  template <typename T> T* take(size_t count) {
+    off = align_up(off, 256);
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += count * sizeof(T);
+    return p;
+  }
+};
+
+struct SearchPlan {
+  int path = NXF_PATH_NONE;
+  int cta_group = 1;
+  int k_eff = 0;     // min(k, n)
+  int k_fetch = 0;   // per-owner keep count in the main kernel
+  int rescore = 0;
+  int cap = 0;
+  int grid = 0;
+  int num_qt = 0, chunks = 1;
+  int64_t tiles_per_chunk = 1, n_tiles = 0;
+  int64_t arena_stride = 0;
+  int64_t owners = 0;
+  // K2
+  int nq_t = 1, rw = 4, stages = 2;
+  size_t k2_smem = 0;
+  int64_t batch = 0;  // queries per launch
+};
+
+}  // namespace
+
+static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int flags, SearchPlan* sp) {
+  SearchPlan& P = *sp;
+  const bool store16 = idx->store_dtype != NXF_F32;
+  P.k_eff = static_cast<int>(std::min<int64_t>(k, idx->n));
+  int path;
+  if (flags & NXF_SEARCH_FORCE_EXACT) path = NXF_PATH_EXACT;
+  else if (flags & NXF_SEARCH_FORCE_STREAM) path = NXF_PATH_STREAM;
+  else if (flags & NXF_SEARCH_FORCE_TENSOR) path = NXF_PATH_TENSOR;
+  else if (nq <= NXF_STREAM_MAX_NQ) path = NXF_PATH_STREAM;
+  else path = store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
+
+  const int64_t row_bytes = idx->ld * dtype_size(idx->store_dtype);
+  if (path == NXF_PATH_STREAM) {
+    // rows per consumer warp per stage: keep a stage <= 48 KB and at least two stages in flight
+    int rw = 4;
+    while (rw > 1 && row_bytes * 8 * rw > 48 * 1024) rw >>= 1;
+    const int nq_t = nq >= 3 ? 4 : (nq == 2 ? 2 : 1);
+    int stages = 4;
+    while (stages > 1 && k2_smem_bytes(idx->ld, dtype_size(idx->store_dtype), nq_t, rw, stages) > 200 * 1024) --stages;
+    if (stages < 2) {
+      if (flags & NXF_SEARCH_FORCE_STREAM) { set_error("nxf_search: rows of %lld bytes are too long for the stream kernel", (long long)row_bytes); return NXF_EUNSUPPORTED; }
+      path = store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
+    } else {
+      P.rw = rw; P.nq_t = nq_t; P.stages = stages;
+      P.k2_smem = k2_smem_bytes(idx->ld, dtype_size(idx->store_dtype), nq_t, rw, stages);
+    }
+  }
+  if (path == NXF_PATH_TENSOR && !store16) {
+    set_error("nxf_search: the tensor-core path needs f16/bf16 storage (index stores f32)");
+    return NXF_EUNSUPPORTED;
+  }
+  P.path = path;
+  P.k_fetch = P.k_eff;
+  P.rescore = 0;
+  if (path == NXF_PATH_STREAM) {
+    const int64_t R = 8 * P.rw;
+    const int64_t n_blocks = ceil_div64(idx->n, R);
+    P.grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(idx->sm_count, n_blocks)));
+    P.cap = std::max(2 * P.k_eff, P.k_eff + 32);
+    P.owners = static_cast<int64_t>(P.grid) * 8 * P.nq_t;
+    P.arena_stride = static_cast<int64_t>(P.grid) * 8 * P.k_eff;
+    P.batch = P.nq_t;
+  } else if (path == NXF_PATH_EXACT) {
+    P.n_tiles = ceil_div64(idx->n, 128);
+    P.num_qt = static_cast<int>(ceil_div64(nq, 128));
+    const int max_grid = 2 * idx->sm_count;
+    plan_units(P.num_qt, P.n_tiles, max_grid, &P.chunks, &P.tiles_per_chunk);
+    P.grid = static_cast<int>(std::min<int64_t>(max_grid, static_cast<int64_t>(P.num_qt) * P.chunks));
+    P.cap = std::max(2 * P.k_eff, P.k_eff + 128);
+    P.owners = static_cast<int64_t>(P.grid) * 128;
+    P.arena_stride = static_cast<int64_t>(P.chunks) * P.k_eff;
+    P.batch = nq;
+  } else {
+    int cg = env_int("NXF_K1_CTA_GROUP", 1);
+    if (flags & NXF_SEARCH_TENSOR_1CTA) cg = 1;
+    if (cg != 2) cg = 1;
+    P.cta_group = cg;
+    // the MMA rounds the queries to the storage type: over-fetch and re-score in fp32 unless the
+    // caller's queries already are of that type (or asked not to)
+    const bool q_exact = (q_dtype == idx->store_dtype);
+    if (!(flags & NXF_SEARCH_NO_RESCORE) && !q_exact) {
+      P.rescore = 1;
+      P.k_fetch = static_cast<int>(std::min<int64_t>(std::min<int64_t>(2 * static_cast<int64_t>(P.k_eff), NXF_MAX_K), idx->n));
+      P.k_fetch = std::max(P.k_fetch, P.k_eff);
+    }
+    P.n_tiles = ceil_div64(idx->n, 256);
+    P.num_qt = static_cast<int>(ceil_div64(nq, 128 * cg));
+    const int clusters = idx->sm_count / cg;
+    plan_units(P.num_qt, P.n_tiles, clusters, &P.chunks, &P.tiles_per_chunk);
+    const int64_t units = static_cast<int64_t>(P.num_qt) * P.chunks;
+    P.grid = static_cast<int>(std::min<int64_t>(clusters, units)) * cg;
+    P.cap = std::max(2 * P.k_fetch, P.k_fetch + 64);
+    P.owners = static_cast<int64_t>(P.grid) * 128;
+    P.arena_stride = static_cast<int64_t>(P.chunks) * P.k_fetch;
+    P.batch = nq;
+  }
+  return NXF_OK;
+}
+
+extern "C" {
+
+int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, int k, float* out_scores,
+               int64_t* out_ids, int out_on_device, int flags, void* stream_) {
+  NXF_REQUIRE(idx != nullptr, "nxf_search: NULL index");
+  NXF_REQUIRE(nq >= 0, "nxf_search: negative query count");
+  NXF_REQUIRE(k >= 1 && k <= NXF_MAX_K, "nxf_search: k=%d outside [1, %d]", k, NXF_MAX_K);
+  if (nq == 0) return NXF_OK;
+  NXF_REQUIRE(q != nullptr && out_scores != nullptr && out_ids != nullptr, "nxf_search: NULL buffer");
+  int rc = check_dtype(q_dtype, "nxf_search(q_dtype)");
+  if (rc) return rc;
+  if (q_ld == 0) q_ld = idx->dim;
+  NXF_REQUIRE(q_ld >= idx->dim, "nxf_search: query stride %lld smaller than dim %d", (long long)q_ld, idx->dim);
+  const int nforce = !!(flags & NXF_SEARCH_FORCE_EXACT) + !!(flags & NXF_SEARCH_FORCE_STREAM) + !!(flags & NXF_SEARCH_FORCE_TENSOR);
+  NXF_REQUIRE(nforce <= 1, "nxf_search: more than one NXF_SEARCH_FORCE_* flag");
+
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const bool l2 = idx->metric == NXF_METRIC_L2;
+  const int64_t total = nq * k;
+
+  // ---- empty index: Faiss fills with -1 / neutral scores ----
+  if (idx->n == 0) {
+    const float fill = l2 ? FLT_MAX : -FLT_MAX;
+    if (!out_on_device) {
+      for (int64_t i = 0; i < total; ++i) { out_scores[i] = fill; out_ids[i] = -1; }
+      return NXF_OK;
+    }
+    // device outputs: run the arena merge over an all-empty arena (qcnt = 0)
+  }
+
+  // plan; if the per-query arena forces several launches, re-plan for the launch size
+  SearchPlan P;
+  int64_t batch = nq;
+  for (int it = 0; it < 8; ++it) {
+    P = SearchPlan();
+    rc = plan_search(idx, batch, q_dtype, k, flags, &P);
+    if (rc) return rc;
+    if (idx->n == 0) break;
+    if (P.path == NXF_PATH_STREAM) { batch = std::min<int64_t>(nq, P.batch); break; }
+    const int64_t budget = (int64_t(6) << 30) << (it >= 6 ? 1 : 0);  // last tries: accept a larger arena
+    const int64_t per_q = std::max<int64_t>(P.arena_stride * 8, 1);
+    const int64_t gran = 128 * P.cta_group;
+    const int64_t max_q = std::max<int64_t>(gran, budget / per_q / gran * gran);
+    if (batch <= max_q || it == 7) break;
+    batch = max_q;
+  }
+  if (idx->n == 0) { P.path = NXF_PATH_NONE; batch = nq; P.arena_stride = 1; P.owners = 0; P.cap = 1; P.k_fetch = 0; P.k_eff = 0; P.rescore = 0; }
+  const bool multi_batch = batch < nq;
+
+  // ---- carve scratch (two passes: size, then pointers) ----
+  const size_t qsz = dtype_size(q_dtype);
+  unsigned char* base = nullptr;
+  float* q_f32 = nullptr; void* q16 = nullptr; void* q_src = nullptr; uint32_t* tau_g = nullptr; uint32_t* qcnt = nullptr;
+  Entry* arena = nullptr; Entry* cand = nullptr; float* o_scores = nullptr; int64_t* o_ids = nullptr;
+  const int64_t nq_pad = round_up64(batch, 256);
+  for (int pass = 0; pass < 2; ++pass) {
+    Carver cv(base);
+    q_src = q_on_device ? nullptr : cv.take<unsigned char>(static_cast<size_t>(batch) * q_ld * qsz);
+    q_f32 = cv.take<float>(static_cast<size_t>(nq_pad) * idx->ld);
+    q16 = (P.path == NXF_PATH_TENSOR) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld) : nullptr;
+    tau_g = cv.take<uint32_t>(static_cast<size_t>(2 * nq_pad));
+    qcnt = tau_g ? tau_g + nq_pad : nullptr;
+    arena = cv.take<Entry>(static_cast<size_t>(batch) * P.arena_stride);
+    cand = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(P.owners, 1)) * P.cap);
+    if (!out_on_device) {
+      o_scores = cv.take<float>(static_cast<size_t>(batch) * k);
+      o_ids = cv.take<int64_t>(static_cast<size_t>(batch) * k);
+    }
+    if (pass == 0) {
+      rc = ensure_scratch(idx, cv.off + 256);
+      if (rc) return rc;
+      base = idx->scratch;
+    }
+  }
+
+  for (int64_t b0 = 0; b0 < nq; b0 += batch) {
+    const int64_t bn = std::min(batch, nq - b0);
+    const unsigned char* qb = static_cast<const unsigned char*>(q) + static_cast<size_t>(b0) * q_ld * qsz;
+    const void* q_dev = qb;
+    if (!q_on_device) {
+      NXF_CUDA(cudaMemcpyAsync(q_src, qb, static_cast<size_t>(bn) * q_ld * qsz, cudaMemcpyHostToDevice, stream));
+      q_dev = q_src;
+    }
+    // queries -> fp32 [bn, ld] (zero padded); 16-bit copy for the MMA
+    rc = launch_convert_rows(q_dev, q_dtype, q_ld, q_f32, NXF_F32, idx->ld, bn, idx->dim, stream);
+    if (rc) return rc;
+    idx->stats.kernel_launches++;
+    if (P.path == NXF_PATH_TENSOR) {
+      rc = launch_convert_rows(q_dev, q_dtype, q_ld, q16, idx->store_dtype, idx->ld, bn, idx->dim, stream);
+      if (rc) return rc;
+      idx->stats.kernel_launches++;
+    }
+    NXF_CUDA(cudaMemsetAsync(tau_g, 0, static_cast<size_t>(2 * nq_pad) * sizeof(uint32_t), stream));
+
+    SinkParams sink;
+    sink.tau_g = tau_g; sink.qcnt = qcnt; sink.arena = arena; sink.cand = cand;
+    sink.arena_stride = P.arena_stride; sink.cap = P.cap; sink.k = P.k_fetch;
+
+    if (P.path == NXF_PATH_STREAM) {
+      // K2 handles up to nq_t queries per launch; a forced stream search of more queries loops
+      for (int64_t s0 = 0; s0 < bn; s0 += P.nq_t) {
+        const int sn = static_cast<int>(std::min<int64_t>(P.nq_t, bn - s0));
+        K2Params kp;
+        kp.q = q_f32 + s0 * idx->ld; kp.ldq = idx->ld; kp.corpus = idx->data; kp.ld = idx->ld;
+        kp.half_norm = l2 ? idx->half_norm : nullptr; kp.n = idx->n; kp.nq = sn; kp.dim = idx->dim; kp.stages = P.stages;
+        kp.n_blocks = ceil_div64(idx->n, 8 * P.rw);
+        kp.sink = sink;
+        kp.sink.tau_g = tau_g + s0; kp.sink.qcnt = qcnt + s0; kp.sink.arena = arena + s0 * P.arena_stride;
+        rc = launch_k2(idx->store_dtype, kp, P.nq_t, P.rw, P.grid, P.k2_smem, stream);
+        if (rc) return rc;
+        idx->stats.kernel_launches++;
+      }
+    } else if (P.path == NXF_PATH_EXACT) {
+      KxParams kp;
+      kp.q = q_f32; kp.ldq = idx->ld; kp.corpus = idx->data; kp.ld = idx->ld; kp.half_norm = l2 ? idx->half_norm : nullptr;
+      kp.n = idx->n; kp.nq = bn; kp.dim = idx->dim;
+      kp.num_qt = static_cast<int>(ceil_div64(bn, 128)); kp.chunks = P.chunks; kp.tiles_per_chunk = P.tiles_per_chunk; kp.n_tiles = P.n_tiles;
+      kp.sink = sink;
+      rc = launch_kx(idx->store_dtype, kp, P.grid, stream);
+      if (rc) return rc;
+      idx->stats.kernel_launches++;
+    } else if (P.path == NXF_PATH_TENSOR) {
+      K1Params kp;
+      kp.n = idx->n; kp.nq = bn; kp.kblocks = static_cast<int>(idx->ld / 64);
+      kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group)); kp.chunks = P.chunks; kp.tiles_per_chunk = P.tiles_per_chunk;
+      kp.n_tiles = P.n_tiles; kp.half_norm = l2 ? idx->half_norm : nullptr;
+      kp.sink = sink;
+      rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, P.grid, stream);
+      if (rc) return rc;
+      idx->stats.kernel_launches++;
+    }
+
+    MergeArenaParams mp;
+    mp.arena = arena; mp.qcnt = qcnt; mp.arena_stride = P.arena_stride; mp.k_fetch = P.k_fetch; mp.k_out = k; mp.metric = idx->metric;
+    mp.rescore = P.rescore; mp.q = q_f32; mp.ldq = idx->ld; mp.corpus = idx->data; mp.ld = idx->ld; mp.dim = idx->dim;
+    mp.id_offset = idx->id_offset;
+    mp.out_scores = out_on_device ? out_scores + b0 * k : o_scores;
+    mp.out_ids = out_on_device ? out_ids + b0 * k : o_ids;
+    rc = launch_merge_arena(idx->store_dtype, mp, bn, stream);
+    if (rc) return rc;
+    idx->stats.kernel_launches++;
+
+    if (!out_on_device) {
+      NXF_CUDA(cudaMemcpyAsync(out_scores + b0 * k, o_scores, static_cast<size_t>(bn) * k * sizeof(float), cudaMemcpyDeviceToHost, stream));
+      NXF_CUDA(cudaMemcpyAsync(out_ids + b0 * k, o_ids, static_cast<size_t>(bn) * k * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+    }
+    if (!out_on_device || !q_on_device || multi_batch) NXF_CUDA(cudaStreamSynchronize(stream));
+  }
+  idx->stats.searches++;
+  idx->stats.last_path = P.path;
+  idx->stats.last_k_fetch = P.k_fetch;
+  idx->stats.last_chunks = P.chunks;
+  idx->stats.last_grid = P.grid;
+  return NXF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// merge + pool (device pointers only)
+// ------------------------------------------------------------------------------------------
+int nxf_merge_topk(const float* scores, const int64_t* ids, int n_lists, int64_t nq, int k, int k_out, int metric, float* out_scores,
+                   int64_t* out_ids, int device, void* stream_) {
+  NXF_REQUIRE(scores && ids && out_scores && out_ids, "nxf_merge_topk: NULL buffer");
+  NXF_REQUIRE(n_lists >= 1 && n_lists <= 4096, "nxf_merge_topk: n_lists=%d outside [1, 4096]", n_lists);
+  NXF_REQUIRE(k >= 1 && k_out >= 1 && k_out <= NXF_MAX_K, "nxf_merge_topk: k=%d k_out=%d (max %d)", k, k_out, NXF_MAX_K);
+  NXF_REQUIRE(static_cast<int64_t>(n_lists) * k < (int64_t(1) << 30), "nxf_merge_topk: too many candidates per query");
+  NXF_REQUIRE(metric == NXF_METRIC_IP || metric == NXF_METRIC_L2, "nxf_merge_topk: unknown metric %d", metric);
+  NXF_REQUIRE(nq >= 0, "nxf_merge_topk: negative nq");
+  DeviceGuard g(device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  MergeListsParams p;
+  p.scores = scores; p.ids = ids; p.n_lists = n_lists; p.nq = nq; p.k = k; p.k_out = k_out; p.metric = metric;
+  p.out_scores = out_scores; p.out_ids = out_ids;
+  return launch_merge_lists(p, static_cast<cudaStream_t>(stream_));
+}
+
+int nxf_pool_normalize(const void* hidden, int h_dtype, const int64_t* mask, int64_t B, int64_t L, int64_t H, int pooling, int normalize,
+                       float eps, void* out, int out_dtype, int device, void* stream_) {
+  NXF_REQUIRE(hidden != nullptr && out != nullptr, "nxf_pool_normalize: NULL buffer");
+  NXF_REQUIRE(B >= 0 && L >= 1 && H >= 1, "nxf_pool_normalize: bad shape B=%lld L=%lld H=%lld", (long long)B, (long long)L, (long long)H);
+  // base.py:378-379: anything but the known rules raises NotImplementedError in the reference
+  NXF_REQUIRE(pooling >= NXF_POOL_CLS && pooling <= NXF_POOL_LAST_ARGMAX, "nxf_pool_normalize: pooling method %d not implemented", pooling);
+  NXF_REQUIRE(pooling == NXF_POOL_CLS || mask != nullptr, "nxf_pool_normalize: this pooling rule needs the attention mask");
+  int rc = check_dtype(h_dtype, "nxf_pool_normalize(h_dtype)");
+  if (rc) return rc;
+  rc = check_dtype(out_dtype, "nxf_pool_normalize(out_dtype)");
+  if (rc) return rc;
+  DeviceGuard g(device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  return launch_pool(hidden, h_dtype, mask, B, L, H, pooling, normalize, eps, out, out_dtype, static_cast<cudaStream_t>(stream_));
+}
+
+}  // extern "C"

@@ -1,0 +1,327 @@
+// merge.cu -- final per-query selection + ordering kernels.
+//
+//   merge_arena_kernel : one CTA per query.  Input: the query's arena slice (unordered candidates
+//       flushed by K1/K2/KX).  Block radix-select to k_fetch, optional exact fp32 re-score of the
+//       survivors against the stored rows (fixes the query-side rounding of the tensor-core pass and
+//       reports true fp32 scores), bitonic sort by (score desc, row asc), write Faiss-shaped rows
+//       [k_out] of (float32 score, int64 id) with -1 / -FLT_MAX padding.
+//   merge_lists_kernel : one CTA per query.  Input: n_lists sorted per-shard lists (the result of the
+//       NCCL all-gather in the row-sharded multi-GPU search, replacing Faiss IndexShards' host merge
+//       behind utils.py:178-183).  Same select + sort on (score, global id).
+#include "params.cuh"
+
+namespace nxf {
+
+namespace mg {
+constexpr int THREADS = 256;
+constexpr int MAXK = NXF_MAX_K;  // 2048
+}  // namespace mg
+
+// ---- block-level helpers -------------------------------------------------------------------
+
+// Finds the exact key of the `need`-th largest of n keys produced by key_at(i).  Returns it in
+// *kth_out and the number of entries equal to kth that must be kept in *need_out (shared memory).
+template <typename KeyAt>
+__device__ __forceinline__ void block_radix_select(int n, int need_in, KeyAt key_at, uint32_t* hist, uint32_t* sh_prefix,
+                                                   int* sh_need) {
+  const int tid = threadIdx.x;
+  if (tid == 0) { *sh_prefix = 0; *sh_need = need_in; }
+  uint32_t mask = 0;
+  __syncthreads();
+#pragma unroll 1
+  for (int pass = 3; pass >= 0; --pass) {
+    const int shift = pass * 8;
+    hist[tid] = 0;  // THREADS == 256
+    __syncthreads();
+    const uint32_t prefix = *sh_prefix;
+    const int need = *sh_need;
+    for (int i = tid; i < n; i += mg::THREADS) {
+      const uint32_t key = key_at(i);
+      if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 0xFF], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {
+      const unsigned lane = tid;
+      uint32_t c[8], lane_sum = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { c[j] = hist[255 - (lane * 8 + j)]; lane_sum += c[j]; }
+      uint32_t incl = lane_sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(kFullMask, incl, o);
+        if (lane >= static_cast<unsigned>(o)) incl += t;
+      }
+      const uint32_t excl = incl - lane_sum;
+      if (excl < static_cast<uint32_t>(need) && static_cast<uint32_t>(need) <= incl) {
+        uint32_t run = excl;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (run < static_cast<uint32_t>(need) && static_cast<uint32_t>(need) <= run + c[j]) {
+            *sh_prefix = prefix | ((255u - (lane * 8 + j)) << shift);
+            *sh_need = need - static_cast<int>(run);
+          }
+          run += c[j];
+        }
+      }
+    }
+    mask |= 0xFFu << shift;
+    __syncthreads();
+  }
+}
+
+// In-place bitonic sort, descending, of P (power of two) 64-bit keys in shared memory, with an
+// optional parallel payload array.
+template <bool PAYLOAD>
+__device__ __forceinline__ void block_bitonic_desc(uint64_t* keys, int64_t* payload, int P) {
+  for (int size = 2; size <= P; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      __syncthreads();
+      for (int t = threadIdx.x; t < (P >> 1); t += mg::THREADS) {
+        const int lo = 2 * t - (t & (stride - 1));
+        const int hi = lo + stride;
+        const bool desc = ((lo & size) == 0);
+        const uint64_t a = keys[lo], b = keys[hi];
+        if ((a < b) == desc) {
+          keys[lo] = b; keys[hi] = a;
+          if (PAYLOAD) { const int64_t x = payload[lo]; payload[lo] = payload[hi]; payload[hi] = x; }
+        }
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ int next_pow2(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// ---- arena merge (+ optional rescore) ---------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaParams p) {
+  extern __shared__ __align__(16) unsigned char dyn_smem[];
+  uint64_t* keys = reinterpret_cast<uint64_t*>(dyn_smem);            // [MAXK]
+  float* q_s = reinterpret_cast<float*>(dyn_smem + mg::MAXK * 8);    // [dim] when rescore / L2
+  __shared__ uint32_t hist[256];
+  __shared__ uint32_t sh_prefix;
+  __shared__ int sh_need, sh_gt, sh_eq;
+  __shared__ float sh_qnorm;
+
+  const int64_t qi = blockIdx.x;
+  const int tid = threadIdx.x;
+  const Entry* __restrict__ src = p.arena + qi * p.arena_stride;
+  int64_t m64 = p.qcnt[qi];
+  if (m64 > p.arena_stride) m64 = p.arena_stride;
+  const int M = static_cast<int>(m64);
+  const int keep = min(M, p.k_fetch);
+  Entry* ent = reinterpret_cast<Entry*>(keys);  // gather target aliases the key array (8 B each)
+
+  const bool need_q = p.rescore || p.metric == NXF_METRIC_L2;
+  if (need_q) {
+    float part = 0.f;
+    for (int d = tid; d < p.dim; d += mg::THREADS) {
+      const float v = p.q[qi * p.ldq + d];
+      q_s[d] = v;
+      part += v * v;
+    }
+    // block reduce |q|^2 (only the L2 output needs it)
+    __shared__ float red[mg::THREADS / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(kFullMask, part, o);
+    if ((tid & 31) == 0) red[tid >> 5] = part;
+    __syncthreads();
+    if (tid == 0) {
+      float s = 0.f;
+      for (int w = 0; w < mg::THREADS / 32; ++w) s += red[w];
+      sh_qnorm = s;
+    }
+  }
+  if (tid == 0) { sh_gt = 0; sh_eq = 0; }
+  __syncthreads();
+
+  if (M > keep) {
+    block_radix_select(M, keep, [&](int i) { return okey(src[i].score); }, hist, &sh_prefix, &sh_need);
+    const uint32_t kth = sh_prefix;
+    const int need = sh_need;
+    const int n_gt = keep - need;
+    for (int i = tid; i < M; i += mg::THREADS) {
+      const Entry e = src[i];
+      const uint32_t key = okey(e.score);
+      if (key > kth) {
+        ent[atomicAdd(&sh_gt, 1)] = e;
+      } else if (key == kth) {
+        const int t = atomicAdd(&sh_eq, 1);
+        if (t < need) ent[n_gt + t] = e;
+      }
+    }
+  } else {
+    for (int i = tid; i < M; i += mg::THREADS) ent[i] = src[i];
+  }
+  __syncthreads();
+
+  // ---- exact fp32 re-score: one warp per candidate ----
+  if (p.rescore) {
+    const T* __restrict__ corpus = reinterpret_cast<const T*>(p.corpus);
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int c = warp; c < keep; c += mg::THREADS / 32) {
+      const int32_t row = ent[c].row;
+      const T* r = corpus + static_cast<int64_t>(row) * p.ld;
+      float dot = 0.f, nn = 0.f;
+      for (int d = lane; d < p.dim; d += 32) {
+        const float v = to_f32<T>(r[d]);
+        dot = fmaf(q_s[d], v, dot);
+        nn = fmaf(v, v, nn);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        dot += __shfl_xor_sync(kFullMask, dot, o);
+        nn += __shfl_xor_sync(kFullMask, nn, o);
+      }
+      if (lane == 0) ent[c].score = (p.metric == NXF_METRIC_L2) ? (dot - 0.5f * nn) : dot;
+    }
+    __syncthreads();
+  }
+
+  // ---- sort by (score desc, row asc) ----
+  const int P = next_pow2(max(keep, 2));
+  // ent[] aliases keys[] slot for slot (8 bytes each): every thread rewrites only the slots it reads
+  for (int i = tid; i < P; i += mg::THREADS) {
+    uint64_t kk = 0;  // below every real key
+    if (i < keep) { const Entry e = ent[i]; kk = sort_key(e.score, e.row); }
+    keys[i] = kk;
+  }
+  block_bitonic_desc<false>(keys, nullptr, P);
+
+  const float qn = (p.metric == NXF_METRIC_L2) ? sh_qnorm : 0.f;
+  for (int j = tid; j < p.k_out; j += mg::THREADS) {
+    float s;
+    int64_t id;
+    if (j < keep) {
+      const uint64_t kk = keys[j];
+      const float sc = sort_key_score(kk);
+      s = (p.metric == NXF_METRIC_L2) ? fmaxf(qn - 2.f * sc, 0.f) : sc;
+      id = static_cast<int64_t>(sort_key_row(kk)) + p.id_offset;
+    } else {
+      s = (p.metric == NXF_METRIC_L2) ? FLT_MAX : -FLT_MAX;
+      id = -1;
+    }
+    p.out_scores[qi * p.k_out + j] = s;
+    p.out_ids[qi * p.k_out + j] = id;
+  }
+}
+
+int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream) {
+  if (nq <= 0) return NXF_OK;
+  const bool need_q = p.rescore || p.metric == NXF_METRIC_L2;
+  const size_t smem = static_cast<size_t>(mg::MAXK) * 8 + (need_q ? static_cast<size_t>(p.dim) * 4 : 0);
+  if (smem > 200 * 1024) { set_error("merge: dim %d too large for the re-score stage", p.dim); return NXF_EUNSUPPORTED; }
+#define NXF_LAUNCH_MERGE(T)                                                                                          \
+  do {                                                                                                               \
+    if (smem > 48 * 1024)                                                                                            \
+      NXF_CUDA(cudaFuncSetAttribute(merge_arena_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    merge_arena_kernel<T><<<static_cast<unsigned>(nq), mg::THREADS, smem, stream>>>(p);                              \
+  } while (0)
+  switch (store_dtype) {
+    case NXF_F32: NXF_LAUNCH_MERGE(float); break;
+    case NXF_F16: NXF_LAUNCH_MERGE(__half); break;
+    case NXF_BF16: NXF_LAUNCH_MERGE(__nv_bfloat16); break;
+    default: set_error("merge: bad storage dtype %d", store_dtype); return NXF_EINVAL;
+  }
+#undef NXF_LAUNCH_MERGE
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
+// ---- multi-list merge (multi-GPU shard merge) ---------------------------------------------------
+__global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(MergeListsParams p) {
+  __shared__ uint64_t keys[mg::MAXK];
+  __shared__ int64_t pay[mg::MAXK];
+  __shared__ uint32_t hist[256];
+  __shared__ uint32_t sh_prefix;
+  __shared__ int sh_need, sh_gt, sh_eq, sh_valid;
+
+  const int64_t qi = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int M = p.n_lists * p.k;
+  const bool l2 = p.metric == NXF_METRIC_L2;
+  auto score_at = [&](int i) -> float {
+    const int l = i / p.k, j = i - l * p.k;
+    return p.scores[(static_cast<int64_t>(l) * p.nq + qi) * p.k + j];
+  };
+  auto id_at = [&](int i) -> int64_t {
+    const int l = i / p.k, j = i - l * p.k;
+    return p.ids[(static_cast<int64_t>(l) * p.nq + qi) * p.k + j];
+  };
+  // key 0 for padding (id < 0) so that it sorts last in either metric
+  auto key_at = [&](int i) -> uint32_t {
+    if (id_at(i) < 0) return 0u;
+    const float s = score_at(i);
+    return okey(l2 ? -s : s);
+  };
+  if (tid == 0) { sh_gt = 0; sh_eq = 0; sh_valid = 0; }
+  __syncthreads();
+  int local_valid = 0;
+  for (int i = tid; i < M; i += mg::THREADS) local_valid += (id_at(i) >= 0);
+  if (local_valid) atomicAdd(&sh_valid, local_valid);
+  __syncthreads();
+  const int keep = min(min(sh_valid, p.k_out), mg::MAXK);
+
+  if (sh_valid > keep) {
+    block_radix_select(M, keep, key_at, hist, &sh_prefix, &sh_need);
+    const uint32_t kth = sh_prefix;
+    const int need = sh_need;
+    const int n_gt = keep - need;
+    for (int i = tid; i < M; i += mg::THREADS) {
+      const uint32_t key = key_at(i);
+      if (key == 0u) continue;
+      int slot = -1;
+      if (key > kth) slot = atomicAdd(&sh_gt, 1);
+      else if (key == kth) { const int t = atomicAdd(&sh_eq, 1); if (t < need) slot = n_gt + t; }
+      if (slot >= 0) {
+        const int64_t id = id_at(i);
+        // tie order: smaller global id first (low 32 bits of the key hold ~id, saturated)
+        const uint32_t low = static_cast<uint32_t>(0x7FFFFFFF) - static_cast<uint32_t>(id > 0x7FFFFFFE ? 0x7FFFFFFE : id);
+        keys[slot] = (static_cast<uint64_t>(key) << 32) | low;
+        pay[slot] = id;
+      }
+    }
+  } else {
+    for (int i = tid; i < M; i += mg::THREADS) {
+      const uint32_t key = key_at(i);
+      if (key == 0u) continue;
+      const int slot = atomicAdd(&sh_gt, 1);
+      const int64_t id = id_at(i);
+      const uint32_t low = static_cast<uint32_t>(0x7FFFFFFF) - static_cast<uint32_t>(id > 0x7FFFFFFE ? 0x7FFFFFFE : id);
+      keys[slot] = (static_cast<uint64_t>(key) << 32) | low;
+      pay[slot] = id;
+    }
+  }
+  __syncthreads();
+  const int P = next_pow2(max(keep, 2));
+  for (int i = keep + tid; i < P; i += mg::THREADS) { keys[i] = 0; pay[i] = -1; }
+  block_bitonic_desc<true>(keys, pay, P);
+  for (int j = tid; j < p.k_out; j += mg::THREADS) {
+    float s;
+    int64_t id;
+    if (j < keep) {
+      const float sc = okey_inv(static_cast<uint32_t>(keys[j] >> 32));
+      s = l2 ? -sc : sc;
+      id = pay[j];
+    } else {
+      s = l2 ? FLT_MAX : -FLT_MAX;
+      id = -1;
+    }
+    p.out_scores[qi * p.k_out + j] = s;
+    p.out_ids[qi * p.k_out + j] = id;
+  }
+}
+
+int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream) {
+  if (p.nq <= 0) return NXF_OK;
+  merge_lists_kernel<<<static_cast<unsigned>(p.nq), mg::THREADS, 0, stream>>>(p);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
+}  // namespace nxf

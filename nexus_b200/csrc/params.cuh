@@ -1,0 +1,95 @@
+// params.cuh -- kernel parameter blocks and launcher prototypes shared between api.cu and the
+// kernel translation units.
+#pragma once
+
+#include "sink.cuh"
+
+namespace nxf {
+
+struct KxParams {
+  const float* q;  // [nq, ldq] fp32, device
+  int64_t ldq;
+  const void* corpus;  // [n, ld] storage type
+  int64_t ld;
+  const float* half_norm;  // 0.5*|c|^2 per row (L2 metric) or nullptr
+  int64_t n;
+  int64_t nq;
+  int dim;
+  int num_qt;
+  int chunks;
+  int64_t tiles_per_chunk;
+  int64_t n_tiles;
+  SinkParams sink;
+};
+
+struct K1Params {
+  int64_t n;    // corpus rows
+  int64_t nq;   // query rows
+  int kblocks;  // ld / 64
+  int num_qt;   // query tiles of 128*CG rows
+  int chunks;
+  int64_t tiles_per_chunk;
+  int64_t n_tiles;  // ceil(n / 256)
+  const float* half_norm;
+  SinkParams sink;
+};
+
+struct K2Params {
+  const float* q;  // [nq, ldq] fp32 device
+  int64_t ldq;
+  const void* corpus;
+  int64_t ld;  // elements per stored row (row bytes are a multiple of 128)
+  const float* half_norm;
+  int64_t n;
+  int nq;
+  int dim;
+  int stages;
+  int64_t n_blocks;  // ceil(n / rows-per-stage)
+  SinkParams sink;
+};
+
+struct MergeArenaParams {
+  const Entry* arena;
+  const uint32_t* qcnt;
+  int64_t arena_stride;
+  int k_fetch;  // candidates to keep before the re-score (<= NXF_MAX_K)
+  int k_out;    // columns of the output
+  int metric;   // NXF_METRIC_*
+  int rescore;  // recompute the kept candidates' scores in fp32 from q and the stored rows
+  const float* q;  // [nq, ldq] fp32 (needed when rescore or metric == L2)
+  int64_t ldq;
+  const void* corpus;
+  int64_t ld;
+  int dim;
+  int64_t id_offset;
+  float* out_scores;  // [nq, k_out]
+  int64_t* out_ids;   // [nq, k_out]
+};
+
+struct MergeListsParams {
+  const float* scores;  // [n_lists, nq, k]
+  const int64_t* ids;   // [n_lists, nq, k]
+  int n_lists;
+  int64_t nq;
+  int k;
+  int k_out;
+  int metric;
+  float* out_scores;
+  int64_t* out_ids;
+};
+
+int launch_kx(int store_dtype, const KxParams& p, int grid, cudaStream_t stream);
+int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, const void* corpus, int64_t ld, const K1Params& p,
+              int grid, cudaStream_t stream);
+int k1_smem_bytes(int cta_group);
+int launch_k2(int store_dtype, const K2Params& p, int nq_t, int rw, int grid, size_t smem, cudaStream_t stream);
+size_t k2_smem_bytes(int64_t ld, int elem_size, int nq_t, int rw, int stages);
+int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
+int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
+int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,
+                        cudaStream_t stream);
+int launch_half_norm(const void* rows, int dtype, int64_t ld, int64_t n, int dim, float* out, cudaStream_t stream);
+int launch_pool(const void* hidden, int h_dtype, const int64_t* mask, int64_t B, int64_t L, int64_t H, int pooling, int normalize,
+                float eps, void* out, int out_dtype, cudaStream_t stream);
+
+}  // namespace nxf

@@ -1,0 +1,208 @@
+"""A minimal ``faiss``-shaped module backed by the B200 engine.
+
+Covers exactly the Faiss names the reference's hot path touches:
+  * ``index_factory(d, "Flat", METRIC_INNER_PRODUCT)``          Nexus/evaluation/text_retrieval/utils.py:176
+  * ``GpuMultipleClonerOptions`` / ``index_cpu_to_all_gpus``      utils.py:180-183
+  * ``IndexFlatIP(d)`` / ``IndexFlatL2(d)``                       Nexus/training/embedder/recommendation/modeling.py:184-190
+  * ``StandardGpuResources()`` / ``index_cpu_to_gpu(res, dev, index)``   modeling.py:182,194; recommendation/base.py:115-116
+  * ``read_index`` / ``write_index``                             serve/inference_service_text_retrieval.py:35; Nexus/inference/utils.py:25
+  * ``faiss.contrib.torch_utils`` (import-only; torch tensors are accepted natively)   modeling.py:9
+
+Everything is exact flat search; ``IVF*`` factory strings (Nexus/inference/utils.py:19) are served by an
+exact index as well -- a recall-superset of IVFFlat(nprobe<nlist) -- and ``nprobe`` is accepted and ignored.
+Objects created "on the CPU" (``IndexFlatIP(d)`` before ``index_cpu_to_gpu``) only record their parameters and
+buffered rows; compute always happens on the GPU: there is no CPU search path.
+"""
+from __future__ import annotations
+
+import os
+import re
+import sys
+import types
+from typing import Optional
+
+import numpy as np
+
+from .flat import FlatIndex, _is_tensor
+from .sharded import ShardedFlatIndex
+
+METRIC_INNER_PRODUCT = 0
+METRIC_L2 = 1
+
+
+def _store_dtype_default() -> str:
+    return os.environ.get("NEXUS_B200_STORE_DTYPE", "f32")
+
+
+class _LazyFlat:
+    """IndexFlat{IP,L2}(d): materialises a device index on first use (device chosen by
+    index_cpu_to_gpu / index_cpu_to_all_gpus, else the current device)."""
+
+    def __init__(self, d: int, metric: int, store_dtype: Optional[str] = None):
+        self.d = int(d)
+        self.metric_type = metric
+        self.nprobe = 1
+        self.is_trained = True
+        self._store_dtype = store_dtype or _store_dtype_default()
+        self._impl = None
+        self._devices = None      # None -> current device; list -> sharded
+
+    def _ensure(self, like=None):
+        if self._impl is None:
+            metric = "l2" if self.metric_type == METRIC_L2 else "ip"
+            if self._devices is not None and len(self._devices) > 1:
+                self._impl = ShardedFlatIndex(self.d, metric, self._store_dtype, devices=self._devices)
+            else:
+                dev = self._devices[0] if self._devices else (like.device.index if (like is not None and _is_tensor(like) and like.is_cuda) else None)
+                self._impl = FlatIndex(self.d, metric, self._store_dtype, device=dev)
+        return self._impl
+
+    @property
+    def ntotal(self) -> int:
+        return 0 if self._impl is None else self._impl.ntotal
+
+    def train(self, x=None):
+        return None
+
+    def add(self, x):
+        self._ensure(x).add(x)
+
+    def search(self, x, k):
+        return self._ensure(x).search(x, k)
+
+    def reset(self):
+        if self._impl is not None:
+            self._impl.reset()
+
+    def reconstruct_n(self, first=0, n=None):
+        impl = self._ensure()
+        if isinstance(impl, ShardedFlatIndex):
+            return np.concatenate([s.reconstruct_n() for s in impl.shards if s.ntotal], axis=0)[first:None if n is None else first + n]
+        return impl.reconstruct_n(first, n)
+
+
+class IndexFlatIP(_LazyFlat):
+    def __init__(self, d: int):
+        super().__init__(d, METRIC_INNER_PRODUCT)
+
+
+class IndexFlatL2(_LazyFlat):
+    def __init__(self, d: int):
+        super().__init__(d, METRIC_L2)
+
+
+def index_factory(d: int, description: str = "Flat", metric: int = METRIC_INNER_PRODUCT):
+    desc = description.strip()
+    if desc != "Flat" and not re.match(r"^(IVF\d+,)?Flat$", desc):
+        raise ValueError(f"index_factory({description!r}): only exact flat indices are implemented")
+    return _LazyFlat(d, metric)
+
+
+class StandardGpuResources:
+    def noTempMemory(self):
+        return None
+
+    def setTempMemory(self, _bytes):
+        return None
+
+
+class GpuMultipleClonerOptions:
+    def __init__(self):
+        self.shard = False
+        self.useFloat16 = False
+
+
+class GpuClonerOptions(GpuMultipleClonerOptions):
+    pass
+
+
+def get_num_gpus() -> int:
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def index_cpu_to_gpu(res, device: int, index, options=None):
+    if index.ntotal:
+        rows = index.reconstruct_n()
+        new = _LazyFlat(index.d, index.metric_type, index._store_dtype)
+        new._devices = [int(device)]
+        new.add(rows)
+        return new
+    index._devices = [int(device)]
+    if options is not None and getattr(options, "useFloat16", False):
+        index._store_dtype = "f16"
+    return index
+
+
+def index_cpu_to_all_gpus(index, co=None, ngpu: int = -1):
+    n = get_num_gpus() if ngpu < 0 else ngpu
+    if n == 0:
+        raise RuntimeError("index_cpu_to_all_gpus: no CUDA device (there is no CPU fallback)")
+    if co is not None and getattr(co, "useFloat16", False):
+        index._store_dtype = "f16"         # utils.py:182
+    rows = index.reconstruct_n() if index.ntotal else None
+    new = _LazyFlat(index.d, index.metric_type, index._store_dtype)
+    new._devices = list(range(n))          # row shards (co.shard = True, utils.py:181); replicas are not implemented
+    if rows is not None:
+        new.add(rows)
+    return new
+
+
+def index_gpu_to_cpu(index):
+    return index
+
+
+_MAGIC = b"NXFLAT01"
+
+
+def write_index(index, path: str) -> None:
+    """Self-describing flat file: magic, d, metric, n, then fp32 rows (np.save-compatible payload)."""
+    rows = index.reconstruct_n() if index.ntotal else np.empty((0, index.d), np.float32)
+    with open(path, "wb") as f:
+        f.write(_MAGIC)
+        np.array([index.d, index.metric_type, rows.shape[0]], dtype=np.int64).tofile(f)
+        rows.astype(np.float32).tofile(f)
+
+
+def read_index(path: str):
+    """Reads files written by :func:`write_index`, and ``.npy`` embedding caches (doc.npy / corpus_embeddings.npy,
+    searcher.py:126-127,144) as inner-product indices."""
+    with open(path, "rb") as f:
+        head = f.read(8)
+        if head == _MAGIC:
+            d, metric, n = np.fromfile(f, dtype=np.int64, count=3)
+            rows = np.fromfile(f, dtype=np.float32, count=int(n) * int(d)).reshape(int(n), int(d))
+            idx = _LazyFlat(int(d), int(metric))
+            if n:
+                idx.add(rows)
+            return idx
+    if head[:6] == b"\x93NUMPY":
+        rows = np.load(path, mmap_mode="r")
+        idx = _LazyFlat(int(rows.shape[1]), METRIC_INNER_PRODUCT)
+        idx.add(np.ascontiguousarray(rows))
+        return idx
+    raise ValueError(f"read_index: {path} is neither a nexus_b200 flat index nor a .npy embedding cache "
+                     "(native Faiss files are not readable without Faiss)")
+
+
+def install_as_faiss(force: bool = False) -> types.ModuleType:
+    """Register this module as ``faiss`` (and ``faiss.contrib.torch_utils``) in ``sys.modules`` so that
+    the reference's ``import faiss`` picks up the B200 engine.  Does nothing if a real faiss is importable
+    unless ``force``."""
+    if not force:
+        try:
+            import faiss as real  # noqa: F401
+            if not getattr(real, "__nexus_b200__", False):
+                return real
+        except ImportError:
+            pass
+    me = sys.modules[__name__]
+    me.__nexus_b200__ = True
+    contrib = types.ModuleType("faiss.contrib")
+    torch_utils = types.ModuleType("faiss.contrib.torch_utils")
+    contrib.torch_utils = torch_utils
+    me.contrib = contrib
+    sys.modules["faiss"] = me
+    sys.modules["faiss.contrib"] = contrib
+    sys.modules["faiss.contrib.torch_utils"] = torch_utils
+    return me

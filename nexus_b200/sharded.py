@@ -1,0 +1,195 @@
+"""Row-sharded multi-GPU flat search.
+
+The reference delegates this to Faiss (``index_cpu_to_all_gpus`` with ``co.shard = True``,
+Nexus/evaluation/text_retrieval/utils.py:178-183): every GPU holds N/G rows, every query goes to every
+shard, per-shard top-k lists are merged on the host.  Here the merge stays on the device:
+
+  * :class:`ShardedFlatIndex`      one process driving G devices (what ``index()`` builds when several GPUs
+                                   are visible, like the reference): per-shard lists are copied peer-to-peer
+                                   over NVLink to the first device and merged by ``nxf_merge_topk``.
+  * :class:`DistributedFlatIndex`  one process per GPU (torchrun): the corpus rows never move after ``add``;
+                                   per-shard ``(score, global id)`` lists are exchanged with ONE NCCL
+                                   all-gather ([Q,k] float32 + [Q,k] int64 per rank) and merged by the same
+                                   kernel on every rank.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .flat import FlatIndex, _is_tensor, merge_topk
+
+
+def shard_bounds(n: int, world: int) -> List[Tuple[int, int]]:
+    """Contiguous row ranges [lo, hi) of ``n`` rows over ``world`` shards; the first ``n % world``
+    shards get one extra row.  Shard g owns global ids [lo_g, hi_g)."""
+    base, rem = divmod(int(n), int(world))
+    out, lo = [], 0
+    for g in range(world):
+        hi = lo + base + (1 if g < rem else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+class ShardedFlatIndex:
+    """One process, several devices (Faiss ``IndexShards`` shape)."""
+
+    def __init__(self, d: int, metric: str = "ip", store_dtype: str = "bf16", devices: Optional[Sequence[int]] = None):
+        import torch
+        if devices is None:
+            devices = list(range(torch.cuda.device_count()))
+        if not devices:
+            raise RuntimeError("ShardedFlatIndex: no CUDA devices")
+        self.devices = [int(x) for x in devices]
+        self.shards = [FlatIndex(d, metric, store_dtype, device=dev) for dev in self.devices]
+        self._d = int(d)
+        self._metric = metric
+        self.nprobe = 1
+        self.is_trained = True
+
+    @property
+    def d(self) -> int:
+        return self._d
+
+    @property
+    def ntotal(self) -> int:
+        return sum(s.ntotal for s in self.shards)
+
+    @property
+    def metric(self) -> str:
+        return self._metric
+
+    def train(self, x=None) -> None:
+        return None
+
+    def reset(self) -> None:
+        for s in self.shards:
+            s.reset()
+
+    def add(self, x) -> None:
+        """First add: rows split contiguously over the devices.  Later adds extend the last shard (ids stay
+        insertion-ordered; the reference adds exactly once, utils.py:189)."""
+        n = int(x.shape[0])
+        if self.ntotal == 0:
+            for (lo, hi), shard in zip(shard_bounds(n, len(self.shards)), self.shards):
+                shard.set_id_offset(lo)
+                if hi > lo:
+                    part = x[lo:hi]
+                    if _is_tensor(part) and part.is_cuda and part.device.index != shard.device:
+                        part = part.to(f"cuda:{shard.device}")
+                    shard.add(part)
+        else:
+            last = self.shards[-1]
+            if last.ntotal == 0:
+                last.set_id_offset(self.ntotal)
+            part = x
+            if _is_tensor(part) and part.is_cuda and part.device.index != last.device:
+                part = part.to(f"cuda:{last.device}")
+            last.add(part)
+
+    def search(self, x, k: int):
+        import torch
+        k = int(k)
+        was_numpy = not _is_tensor(x)
+        xt = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float32) if np.asarray(x).dtype not in (np.float16, np.float32) else np.asarray(x))) if was_numpy else x
+        was_cuda = (not was_numpy) and xt.is_cuda
+        home = self.devices[0] if not was_cuda else xt.device.index
+        parts_d, parts_i = [], []
+        # launch every shard's search (asynchronous on its own device), then gather over NVLink
+        for shard in self.shards:
+            if shard.ntotal == 0:
+                continue
+            q = xt.to(f"cuda:{shard.device}", non_blocking=True)
+            with torch.cuda.device(shard.device):
+                D, I = shard.search(q, k)
+            parts_d.append(D)
+            parts_i.append(I)
+        if not parts_d:
+            nq = xt.shape[0]
+            D = torch.full((nq, k), -torch.finfo(torch.float32).max if self._metric != "l2" else torch.finfo(torch.float32).max)
+            I = torch.full((nq, k), -1, dtype=torch.int64)
+            return (D.numpy(), I.numpy()) if was_numpy else (D.to(xt.device), I.to(xt.device))
+        for shard_d in parts_d:
+            torch.cuda.current_stream(shard_d.device).synchronize()
+        with torch.cuda.device(home):
+            Ds = torch.stack([t.to(f"cuda:{home}") for t in parts_d])
+            Is = torch.stack([t.to(f"cuda:{home}") for t in parts_i])
+            D, I = merge_topk(Ds, Is, k, "l2" if self._metric == "l2" else "ip")
+        if was_numpy:
+            return D.cpu().numpy(), I.cpu().numpy()
+        if not was_cuda:
+            return D.cpu(), I.cpu()
+        return D, I
+
+
+class DistributedFlatIndex:
+    """One process per GPU over ``torch.distributed`` (NCCL).  Rank r holds shard r."""
+
+    def __init__(self, d: int, metric: str = "ip", store_dtype: str = "bf16", device=None, group=None):
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            raise RuntimeError("DistributedFlatIndex needs an initialised torch.distributed process group")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        if device is None:
+            device = torch.cuda.current_device()
+        self.local = FlatIndex(d, metric, store_dtype, device=device)
+        self._metric = metric
+        self._ntotal_global = 0
+
+    @property
+    def ntotal(self) -> int:
+        return self._ntotal_global
+
+    @property
+    def d(self) -> int:
+        return self.local.d
+
+    def add_global(self, x) -> None:
+        """Every rank passes the SAME [N, D] rows (or a lazily sliceable view of them, e.g. an np.memmap);
+        rank r keeps rows shard_bounds(N, world)[r] and nothing else."""
+        if self._ntotal_global != 0:
+            raise RuntimeError("add_global: the sharded index is already populated (reset() first)")
+        n = int(x.shape[0])
+        lo, hi = shard_bounds(n, self.world)[self.rank]
+        self.local.set_id_offset(lo)
+        if hi > lo:
+            self.local.add(x[lo:hi])
+        self._ntotal_global = n
+
+    def add_local(self, x_local, global_offset: int, n_global: int) -> None:
+        """Rank-local rows that already are this rank's shard (e.g. straight from a data-parallel encoder:
+        the embeddings are never all-gathered, unlike mmeb_v2/eval_embedding.py:127-131)."""
+        self.local.set_id_offset(int(global_offset))
+        self.local.add(x_local)
+        self._ntotal_global = int(n_global)
+
+    def reset(self) -> None:
+        self.local.reset()
+        self._ntotal_global = 0
+
+    def search(self, q, k: int, gather=None, merge=None):
+        """``q``: the same [Q, D] CUDA tensor on every rank.  Returns the merged ``(D, I)`` on every rank.
+        ``gather`` / ``merge`` are injection points for the CPU (gloo) tests of the exchange logic."""
+        D, I = self.local.search(q, int(k))
+        Ds, Is = (gather or all_gather_lists)(D, I, self.world, self.group)
+        return (merge or merge_topk)(Ds, Is, int(k), "l2" if self._metric == "l2" else "ip")
+
+
+def all_gather_lists(D, I, world: int, group=None):
+    """ONE collective per tensor: [Q,k] -> [world, Q,k].  NCCL on GPUs; gloo in the CPU tests."""
+    import torch
+    import torch.distributed as dist
+    Ds = torch.empty((world,) + tuple(D.shape), dtype=D.dtype, device=D.device)
+    Is = torch.empty((world,) + tuple(I.shape), dtype=I.dtype, device=I.device)
+    if hasattr(dist, "all_gather_into_tensor") and D.is_cuda:
+        dist.all_gather_into_tensor(Ds, D.contiguous(), group=group)
+        dist.all_gather_into_tensor(Is, I.contiguous(), group=group)
+    else:
+        dist.all_gather(list(Ds.unbind(0)), D.contiguous(), group=group)
+        dist.all_gather(list(Is.unbind(0)), I.contiguous(), group=group)
+    return Ds, Is

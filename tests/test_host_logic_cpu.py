@@ -1,0 +1,99 @@
+"""CPU: host-side logic (sharding arithmetic, argument parsing, faiss shim plumbing, file formats)."""
+import os
+
+import numpy as np
+import pytest
+
+from nexus_b200 import shard_bounds
+from nexus_b200.flat import parse_device, parse_store_dtype, _as_rows
+from nexus_b200 import _lib as L
+
+
+def test_shard_bounds_cover_and_balance():
+    for n in [0, 1, 7, 8, 9, 8_841_823, 21_000_000]:
+        for g in [1, 2, 3, 4, 8]:
+            b = shard_bounds(n, g)
+            assert b[0][0] == 0 and b[-1][1] == n and len(b) == g
+            assert all(b[i][1] == b[i + 1][0] for i in range(g - 1))
+            sizes = [hi - lo for lo, hi in b]
+            assert max(sizes) - min(sizes) <= 1
+    assert shard_bounds(21_000_000, 8)[3] == (7_875_000, 10_500_000)     # config 3: 2 625 000 rows per GPU
+
+
+def test_parse_device_and_dtype():
+    assert parse_device(3) == 3 and parse_device("cuda:5") == 5 and parse_device("2") == 2
+    with pytest.raises(ValueError):
+        parse_device("cpu")
+    assert parse_store_dtype("bf16") == L.BF16 and parse_store_dtype("float16") == L.F16 and parse_store_dtype("fp32") == L.F32
+    import torch
+    assert parse_store_dtype(torch.bfloat16) == L.BF16
+    with pytest.raises(ValueError):
+        parse_store_dtype("int8")
+
+
+def test_row_views():
+    import torch
+    a = np.arange(12, dtype=np.float64).reshape(3, 4)
+    b = _as_rows(a, 4, "t")
+    assert b.dtype == L.F32 and b.ld == 4 and b.n == 3 and b.on_device == 0      # reference casts to fp32 (utils.py:169)
+    b = _as_rows(a.astype(np.float16)[:, :], 4, "t")
+    assert b.dtype == L.F16
+    b = _as_rows(np.zeros(4, np.float32), 4, "t")
+    assert b.n == 1
+    t = torch.zeros(5, 8, dtype=torch.bfloat16)
+    b = _as_rows(t[:, :4], None, "t")          # strided view keeps its row stride
+    assert b.dtype == L.BF16 and b.ld == 8 and b.d == 4
+    with pytest.raises(ValueError):
+        _as_rows(a, 5, "t")
+    with pytest.raises(ValueError):
+        _as_rows(np.zeros((2, 2, 2)), None, "t")
+
+
+def test_faiss_shim_surface():
+    from nexus_b200 import faiss_shim as F
+    idx = F.index_factory(16, "Flat", F.METRIC_INNER_PRODUCT)
+    assert idx.d == 16 and idx.ntotal == 0 and idx.is_trained
+    idx.nprobe = 10                              # recommendation/base.py:117
+    idx.train(np.zeros((2, 16), np.float32))     # utils.py:188: no-op
+    assert F.IndexFlatL2(8).metric_type == F.METRIC_L2 and F.IndexFlatIP(8).metric_type == F.METRIC_INNER_PRODUCT
+    co = F.GpuMultipleClonerOptions()
+    co.shard = True
+    co.useFloat16 = True
+    F.StandardGpuResources()
+    with pytest.raises(ValueError):
+        F.index_factory(16, "HNSW32")
+    F.index_factory(16, "IVF100,Flat")           # served exactly (Nexus/inference/utils.py:19)
+
+
+def test_index_file_roundtrip_header(tmp_path):
+    from nexus_b200 import faiss_shim as F
+    p = tmp_path / "x.nxf"
+
+    class Fake:
+        d, metric_type, ntotal = 4, 0, 3
+        def reconstruct_n(self):
+            return np.arange(12, dtype=np.float32).reshape(3, 4)
+    F.write_index(Fake(), str(p))
+    raw = open(p, "rb").read()
+    assert raw[:8] == b"NXFLAT01" and len(raw) == 8 + 24 + 48
+    with pytest.raises(ValueError):
+        bad = tmp_path / "bad.bin"
+        bad.write_bytes(b"0123456789abcdef")
+        F.read_index(str(bad))
+
+
+def test_install_as_faiss_registers_modules():
+    import sys
+    from nexus_b200 import faiss_shim as F
+    saved = {k: sys.modules.get(k) for k in ("faiss", "faiss.contrib", "faiss.contrib.torch_utils")}
+    try:
+        m = F.install_as_faiss(force=True)
+        import faiss
+        import faiss.contrib.torch_utils  # noqa: F401  (modeling.py:8-9)
+        assert faiss is m and hasattr(faiss, "IndexFlatIP") and hasattr(faiss, "index_cpu_to_all_gpus")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
