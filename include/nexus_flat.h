@@ -109,6 +109,8 @@ typedef struct nxf_stats {
   int32_t last_grid;       /* CTAs of the last main kernel */
   int64_t scratch_bytes;   /* device scratch currently held */
   int64_t storage_bytes;   /* device bytes of row storage currently held */
+  int64_t main_kernel_count; /* main search kernels timed since nxf_set_profiling(idx, 1) */
+  double main_kernel_ms;     /* their summed device time (CUDA events on the launching stream) */
 } nxf_stats;
 
 /* ---- library ---- */
@@ -134,6 +136,10 @@ NXF_API int nxf_device(const nxf_index* idx);
 /* ids reported by nxf_search are (row + offset): a row shard sets its first global row here */
 NXF_API int nxf_set_id_offset(nxf_index* idx, int64_t offset);
 NXF_API int nxf_get_stats(const nxf_index* idx, nxf_stats* out);
+/* enable != 0: bracket every main search kernel (K1/K2/KX) with CUDA events on its stream; the summed
+ * durations are folded into nxf_stats by nxf_get_stats (which then synchronises those events).
+ * Enabling resets the two counters. */
+NXF_API int nxf_set_profiling(nxf_index* idx, int enable);
 
 /* ---- build / add ---- */
 /* Append n rows of `dim` elements of type src_dtype, row stride `src_ld` elements (0 = dim).

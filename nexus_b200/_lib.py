@@ -31,6 +31,7 @@ PATH_NAMES = {0: "none", 1: "stream", 2: "tensor", 3: "exact"}
 EXPORTS = [
     "nxf_version", "nxf_last_error", "nxf_device_count", "nxf_create", "nxf_destroy", "nxf_reset", "nxf_reserve",
     "nxf_ntotal", "nxf_dim", "nxf_metric", "nxf_store_dtype", "nxf_device", "nxf_set_id_offset", "nxf_get_stats",
+    "nxf_set_profiling",
     "nxf_add", "nxf_reconstruct", "nxf_search", "nxf_merge_topk", "nxf_pool_normalize",
 ]
 
@@ -40,6 +41,7 @@ class Stats(C.Structure):
         ("kernel_launches", C.c_int64), ("searches", C.c_int64), ("rows_added", C.c_int64),
         ("last_path", C.c_int32), ("last_k_fetch", C.c_int32), ("last_chunks", C.c_int32), ("last_grid", C.c_int32),
         ("scratch_bytes", C.c_int64), ("storage_bytes", C.c_int64),
+        ("main_kernel_count", C.c_int64), ("main_kernel_ms", C.c_double),
     ]
 
 
@@ -82,6 +84,7 @@ def load() -> C.CDLL:
             getattr(lib, name).restype = i32
         lib.nxf_set_id_offset.argtypes = [vp, i64]
         lib.nxf_get_stats.argtypes = [vp, C.POINTER(Stats)]
+        lib.nxf_set_profiling.argtypes = [vp, i32]
         lib.nxf_add.argtypes = [vp, vp, i64, i32, i64, i32, vp]
         lib.nxf_reconstruct.argtypes = [vp, i64, i64, vp, i32, vp]
         lib.nxf_search.argtypes = [vp, vp, i64, i32, i64, i32, i32, vp, vp, i32, i32, vp]

@@ -6,6 +6,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <vector>
 
 #include "params.cuh"
 
@@ -53,6 +54,8 @@ struct nxf_index {
   unsigned char* pinned = nullptr;
   size_t pinned_bytes = 0;
   nxf_stats stats{};
+  bool profiling = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;  // pending (start, stop) pairs
   std::mutex mu;
 };
 
@@ -243,8 +246,37 @@ int nxf_set_id_offset(nxf_index* idx, int64_t offset) {
   return NXF_OK;
 }
 
-int nxf_get_stats(const nxf_index* idx, nxf_stats* out) {
+static void fold_profile_events(nxf_index* idx) {
+  for (auto& pr : idx->prof_events) {
+    float ms = 0.f;
+    if (cudaEventSynchronize(pr.second) == cudaSuccess && cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) {
+      idx->stats.main_kernel_ms += ms;
+      idx->stats.main_kernel_count++;
+    }
+    cudaEventDestroy(pr.first);
+    cudaEventDestroy(pr.second);
+  }
+  idx->prof_events.clear();
+}
+
+int nxf_set_profiling(nxf_index* idx, int enable) {
+  NXF_REQUIRE(idx != nullptr, "nxf_set_profiling: NULL index");
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  fold_profile_events(idx);
+  idx->profiling = enable != 0;
+  if (enable) { idx->stats.main_kernel_ms = 0.0; idx->stats.main_kernel_count = 0; }
+  return NXF_OK;
+}
+
+int nxf_get_stats(const nxf_index* idx_c, nxf_stats* out) {
+  nxf_index* idx = const_cast<nxf_index*>(idx_c);
   NXF_REQUIRE(idx != nullptr && out != nullptr, "nxf_get_stats: NULL argument");
+  if (!idx->prof_events.empty()) {
+    std::lock_guard<std::mutex> lk(idx->mu);
+    DeviceGuard g(idx->device);
+    fold_profile_events(idx);
+  }
   *out = idx->stats;
   return NXF_OK;
 }
@@ -442,7 +474,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.arena_stride = static_cast<int64_t>(P.chunks) * P.k_eff;
     P.batch = nq;
   } else {
-    int cg = env_int("NXF_K1_CTA_GROUP", 1);
+    int cg = env_int("NXF_K1_CTA_GROUP", 2);
     if (flags & NXF_SEARCH_TENSOR_1CTA) cg = 1;
     if (cg != 2) cg = 1;
     P.cta_group = cg;
@@ -565,6 +597,12 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     }
     NXF_CUDA(cudaMemsetAsync(tau_g, 0, static_cast<size_t>(2 * nq_pad) * sizeof(uint32_t), stream));
 
+    cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+    if (idx->profiling && P.path != NXF_PATH_NONE) {
+      NXF_CUDA(cudaEventCreate(&pe0));
+      NXF_CUDA(cudaEventCreate(&pe1));
+      NXF_CUDA(cudaEventRecord(pe0, stream));
+    }
     SinkParams sink;
     sink.tau_g = tau_g; sink.qcnt = qcnt; sink.arena = arena; sink.cand = cand;
     sink.arena_stride = P.arena_stride; sink.cap = P.cap; sink.k = P.k_fetch;
@@ -603,6 +641,10 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       idx->stats.kernel_launches++;
     }
 
+    if (pe0) {
+      NXF_CUDA(cudaEventRecord(pe1, stream));
+      idx->prof_events.emplace_back(pe0, pe1);
+    }
     MergeArenaParams mp;
     mp.arena = arena; mp.qcnt = qcnt; mp.arena_stride = P.arena_stride; mp.k_fetch = P.k_fetch; mp.k_out = k; mp.metric = idx->metric;
     mp.rescore = P.rescore; mp.q = q_f32; mp.ldq = idx->ld; mp.corpus = idx->data; mp.ld = idx->ld; mp.dim = idx->dim;

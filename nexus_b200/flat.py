@@ -199,7 +199,7 @@ class FlatIndex:
         return self.reconstruct_n(i, 1)[0]
 
     # ---- search ----
-    def search(self, x, k: int, flags: Optional[int] = None) -> Tuple:
+    def search(self, x, k: int, flags: Optional[int] = None, out=None) -> Tuple:
         """``(D float32 [n,k], I int64 [n,k])``, rows best-first, ``-1`` padding when k > ntotal."""
         b = _as_rows(x, self.d, "search")
         k = int(k)
@@ -214,14 +214,23 @@ class FlatIndex:
                 I = torch.empty((b.n, k), dtype=torch.int64, device=b.keep.device)
                 L.check(self._lib.nxf_search(self._h, b.ptr, b.n, b.dtype, b.ld, 1, k, D.data_ptr(), I.data_ptr(), 1, flags, stream))
                 return D, I
-            D = torch.empty((b.n, k), dtype=torch.float32)
-            I = torch.empty((b.n, k), dtype=torch.int64)
+            if out is not None:       # caller-provided (e.g. pinned) CPU result tensors
+                D, I = out
+                assert tuple(D.shape) == (b.n, k) and tuple(I.shape) == (b.n, k) and D.is_contiguous() and I.is_contiguous()
+                assert D.dtype == torch.float32 and I.dtype == torch.int64 and not D.is_cuda and not I.is_cuda
+            else:
+                D = torch.empty((b.n, k), dtype=torch.float32)
+                I = torch.empty((b.n, k), dtype=torch.int64)
             L.check(self._lib.nxf_search(self._h, b.ptr, b.n, b.dtype, b.ld, 0, k, D.data_ptr(), I.data_ptr(), 0, flags, stream))
             return D, I
         D = np.empty((b.n, k), dtype=np.float32)
         I = np.empty((b.n, k), dtype=np.int64)
         L.check(self._lib.nxf_search(self._h, b.ptr, b.n, b.dtype, b.ld, 0, k, D.ctypes.data, I.ctypes.data, 0, flags, stream))
         return D, I
+
+    def set_profiling(self, enable: bool = True) -> None:
+        """Time every main search kernel with CUDA events on its stream (read back through stats())."""
+        L.check(self._lib.nxf_set_profiling(self._h, 1 if enable else 0))
 
     def stats(self) -> dict:
         st = L.Stats()
