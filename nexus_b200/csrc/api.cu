@@ -483,7 +483,11 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     const bool q_exact = (q_dtype == idx->store_dtype);
     if (!(flags & NXF_SEARCH_NO_RESCORE) && !q_exact) {
       P.rescore = 1;
-      P.k_fetch = static_cast<int>(std::min<int64_t>(std::min<int64_t>(2 * static_cast<int64_t>(P.k_eff), NXF_MAX_K), idx->n));
+      // over-fetch k' = k + max(16, k/4): the bf16 rounding of a unit query perturbs a score by ~6e-5 (1 sigma) while
+      // the gap between ranks k and 1.25k of a large corpus is tens of sigma (DESIGN.md "over-fetch")
+      int64_t kf = static_cast<int64_t>(P.k_eff) + std::max<int64_t>(16, (P.k_eff + 3) / 4);
+      kf = (kf + 7) / 8 * 8;
+      P.k_fetch = static_cast<int>(std::min<int64_t>(std::min<int64_t>(kf, NXF_MAX_K), idx->n));
       P.k_fetch = std::max(P.k_fetch, P.k_eff);
     }
     P.n_tiles = ceil_div64(idx->n, 256);
@@ -635,6 +639,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.n = idx->n; kp.nq = bn; kp.kblocks = static_cast<int>(idx->ld / 64);
       kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group)); kp.chunks = P.chunks; kp.tiles_per_chunk = P.tiles_per_chunk;
       kp.n_tiles = P.n_tiles; kp.half_norm = l2 ? idx->half_norm : nullptr;
+      kp.debug = env_int("NXF_K1_DEBUG", 0);
       kp.sink = sink;
       rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, P.grid, stream);
       if (rc) return rc;

@@ -31,6 +31,7 @@ struct K1Params {
   int64_t tiles_per_chunk;
   int64_t n_tiles;  // ceil(n / 256)
   const float* half_norm;
+  int debug;  // bit0: epilogue skips the selection; bit1: epilogue skips the TMEM loads too (pipeline timing only)
   SinkParams sink;
 };
 

@@ -131,11 +131,11 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int64_t t1 = min(t0 + p.tiles_per_chunk, p.n_tiles);
         for (int64_t t = t0; t < t1; ++t, ++iter) {
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
-          if (CG == 2) mbar_wait_cluster(&tempty[as], aph ^ 1); else mbar_wait(&tempty[as], aph ^ 1);
+          mbar_wait(&tempty[as], aph ^ 1);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * BLOCK_N;
           for (int kb = 0; kb < p.kblocks; ++kb) {
-            if (CG == 2) mbar_wait_cluster(&full[s], ph); else mbar_wait(&full[s], ph);
+            mbar_wait(&full[s], ph);
             tc_fence_after();
             const uint64_t a_desc = umma_desc_sw128(smem_u32(a_ptr(s)));
             const uint64_t b_desc = umma_desc_sw128(smem_u32(b_ptr(s)));
@@ -153,10 +153,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // do not tear the barriers down while the last remote arrivals may still be in flight
       if (iter > 0) {
         const uint32_t last = iter - 1;
-        if (CG == 2) mbar_wait_cluster(&tempty[last & 1], (last >> 1) & 1); else mbar_wait(&tempty[last & 1], (last >> 1) & 1);
+        mbar_wait(&tempty[last & 1], (last >> 1) & 1);
         if (iter > 1) {
           const uint32_t prev = iter - 2;
-          if (CG == 2) mbar_wait_cluster(&tempty[prev & 1], (prev >> 1) & 1); else mbar_wait(&tempty[prev & 1], (prev >> 1) & 1);
+          mbar_wait(&tempty[prev & 1], (prev >> 1) & 1);
         }
       }
     }
@@ -183,18 +183,24 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       const bool valid = qrow < p.nq;
       float tau = valid ? tau_load(p.sink.tau_g, qrow) : INFINITY;  // padded rows accept nothing
       int cnt = 0;
+      float tau_next = tau;
 
       for (int64_t t = t0; t < t1; ++t, ++iter) {
         const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
-        if (valid) tau = fmaxf(tau, tau_load(p.sink.tau_g, qrow));  // other CTAs' progress on this query
+        tau = fmaxf(tau, tau_next);  // other CTAs' progress on this query (loaded during the previous tile)
         mbar_wait(&tfull[as], aph);
         tc_fence_after();
         const int32_t col0 = static_cast<int32_t>(t * BLOCK_N);
 #pragma unroll 1
         for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
           uint32_t vr[32];
-          tmem_ld32(taddr + as * BLOCK_N + ch * 32, vr);
-          tmem_ld_wait();
+          if (!(p.debug & 2)) {
+            tmem_ld32(taddr + as * BLOCK_N + ch * 32, vr);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) vr[j] = 0;
+          }
           if (ch == BLOCK_N / 32 - 1) {
             // accumulator fully read: hand the TMEM buffer back to the MMA issuer
             tc_fence_before();
@@ -203,6 +209,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]);
             }
           }
+          if (p.debug & 1) continue;
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
@@ -211,18 +218,27 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] -= p.half_norm[min(cbase + j, n_rows - 1)];
           }
-          float m = fmax3(v[0], v[1], v[2]);
+          // four 8-wide group maxima (3-input max), then the chunk maximum: 18 instructions for 32 scores
+          float gm[4];
 #pragma unroll
-          for (int j = 3; j < 31; j += 2) m = fmax3(m, v[j], v[j + 1]);
-          m = fmaxf(m, v[31]);
+          for (int g8 = 0; g8 < 4; ++g8) {
+            const int b8 = g8 * 8;
+            gm[g8] = fmaxf(fmax3(fmax3(v[b8], v[b8 + 1], v[b8 + 2]), v[b8 + 3], v[b8 + 4]), fmax3(v[b8 + 5], v[b8 + 6], v[b8 + 7]));
+          }
+          const float m = fmaxf(fmax3(gm[0], gm[1], gm[2]), gm[3]);
           const bool hit = m > tau;
           if (__any_sync(kFullMask, hit)) {
             if (hit) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                if (v[j] > tau && cbase + j < n_rows) {
-                  Entry e; e.score = v[j]; e.row = cbase + j;
-                  my_buf[cnt++] = e;
+              for (int g8 = 0; g8 < 4; ++g8) {
+                if (gm[g8] > tau) {
+#pragma unroll
+                  for (int j = g8 * 8; j < g8 * 8 + 8; ++j) {
+                    if (v[j] > tau && cbase + j < n_rows) {
+                      Entry e; e.score = v[j]; e.row = cbase + j;
+                      my_buf[cnt++] = e;
+                    }
+                  }
                 }
               }
             }
@@ -242,6 +258,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
           }
         }
+        if (valid) tau_next = tau_load(p.sink.tau_g, qrow);
       }
 
       // ---- unit end: prune to k, publish, flush the 32 rows of this warp to the arena ----

@@ -50,5 +50,7 @@ def run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, atol=1e-6, min_r
         ref_s, ref_i = oracle.blocked_l2_search(cs, xs, k, pad=True)
         rep = oracle.check_topk(ref_s, ref_i, D, I, None, None, rtol=rtol, atol=atol, tie_tol=1e-4, descending=False)
     assert rep.ok, (st, rep.messages[:8], rep)
-    assert rep.recall >= min_recall, rep
+    # ids that differ only by a tie within tolerance are not recall losses
+    total = max(1, int((I >= 0).sum()))
+    assert rep.recall + rep.tie_swaps / total >= min_recall, rep
     return idx, D, I, rep, st
