@@ -411,6 +411,9 @@ struct SearchPlan {
   int grid = 0;
   int num_qt = 0, chunks = 1;
   int64_t tiles_per_chunk = 1, n_tiles = 0;
+  // K1 threshold-seeding pass over tiles [0, seed_tiles)
+  int64_t seed_tiles = 0, seed_tpc = 1;
+  int seed_chunks = 0, seed_grid = 0;
   int64_t arena_stride = 0;
   int64_t owners = 0;
   // K2
@@ -474,9 +477,10 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.arena_stride = static_cast<int64_t>(P.chunks) * P.k_eff;
     P.batch = nq;
   } else {
-    int cg = env_int("NXF_K1_CTA_GROUP", 2);
+    // one 128-row query tile: a CTA pair (M = 256) would spend half its MMAs on padding
+    int cg = env_int("NXF_K1_CTA_GROUP", 0);
+    if (cg != 1 && cg != 2) cg = (nq <= 128) ? 1 : 2;
     if (flags & NXF_SEARCH_TENSOR_1CTA) cg = 1;
-    if (cg != 2) cg = 1;
     P.cta_group = cg;
     // the MMA rounds the queries to the storage type: over-fetch and re-score in fp32 unless the
     // caller's queries already are of that type (or asked not to)
@@ -493,12 +497,19 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.n_tiles = ceil_div64(idx->n, 256);
     P.num_qt = static_cast<int>(ceil_div64(nq, 128 * cg));
     const int clusters = idx->sm_count / cg;
-    plan_units(P.num_qt, P.n_tiles, clusters, &P.chunks, &P.tiles_per_chunk);
+    // threshold seeding (DESIGN.md "seed pass"): search the first ~1/64 of the corpus, publish each query's exact
+    // k'-th best of that sample as its threshold, then run the main pass over the rest
+    if (P.n_tiles >= 128 && !env_int("NXF_K1_NO_SEED", 0)) {
+      P.seed_tiles = std::max<int64_t>(P.n_tiles / 64, std::min<int64_t>(P.n_tiles / 8, clusters));
+      plan_units(P.num_qt, P.seed_tiles, clusters, &P.seed_chunks, &P.seed_tpc);
+      P.seed_grid = static_cast<int>(std::min<int64_t>(clusters, static_cast<int64_t>(P.num_qt) * P.seed_chunks)) * cg;
+    }
+    plan_units(P.num_qt, P.n_tiles - P.seed_tiles, clusters, &P.chunks, &P.tiles_per_chunk);
     const int64_t units = static_cast<int64_t>(P.num_qt) * P.chunks;
     P.grid = static_cast<int>(std::min<int64_t>(clusters, units)) * cg;
     P.cap = std::max(2 * P.k_fetch, P.k_fetch + 64);
-    P.owners = static_cast<int64_t>(P.grid) * 128;
-    P.arena_stride = static_cast<int64_t>(P.chunks) * P.k_fetch;
+    P.owners = static_cast<int64_t>(std::max(P.grid, P.seed_grid)) * 128;
+    P.arena_stride = static_cast<int64_t>(P.chunks + P.seed_chunks) * P.k_fetch;
     P.batch = nq;
   }
   return NXF_OK;
@@ -637,10 +648,19 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     } else if (P.path == NXF_PATH_TENSOR) {
       K1Params kp;
       kp.n = idx->n; kp.nq = bn; kp.kblocks = static_cast<int>(idx->ld / 64);
-      kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group)); kp.chunks = P.chunks; kp.tiles_per_chunk = P.tiles_per_chunk;
-      kp.n_tiles = P.n_tiles; kp.half_norm = l2 ? idx->half_norm : nullptr;
+      kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group));
+      kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
       kp.sink = sink;
+      if (P.seed_tiles > 0) {
+        kp.tile_begin = 0; kp.n_tiles = P.seed_tiles; kp.chunks = P.seed_chunks; kp.tiles_per_chunk = P.seed_tpc;
+        rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, P.seed_grid, stream);
+        if (rc) return rc;
+        rc = launch_seed_tau(arena, qcnt, P.arena_stride, P.k_fetch, tau_g, bn, stream);
+        if (rc) return rc;
+        idx->stats.kernel_launches += 2;
+      }
+      kp.tile_begin = P.seed_tiles; kp.n_tiles = P.n_tiles; kp.chunks = P.chunks; kp.tiles_per_chunk = P.tiles_per_chunk;
       rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, P.grid, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;

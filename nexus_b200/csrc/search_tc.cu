@@ -95,7 +95,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       for (int64_t u = cluster_id; u < num_units; u += num_clusters) {
         const int qt = static_cast<int>(u % p.num_qt);
         const int64_t c = u / p.num_qt;
-        const int64_t t0 = c * p.tiles_per_chunk;
+        const int64_t t0 = p.tile_begin + c * p.tiles_per_chunk;
         const int64_t t1 = min(t0 + p.tiles_per_chunk, p.n_tiles);
         const int32_t q_row0 = static_cast<int32_t>((static_cast<int64_t>(qt) * CG + rank) * BLOCK_M);
         for (int64_t t = t0; t < t1; ++t) {
@@ -127,7 +127,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       uint32_t iter = 0;
       for (int64_t u = cluster_id; u < num_units; u += num_clusters) {
         const int64_t c = u / p.num_qt;
-        const int64_t t0 = c * p.tiles_per_chunk;
+        const int64_t t0 = p.tile_begin + c * p.tiles_per_chunk;
         const int64_t t1 = min(t0 + p.tiles_per_chunk, p.n_tiles);
         for (int64_t t = t0; t < t1; ++t, ++iter) {
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
@@ -176,7 +176,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     for (int64_t u = cluster_id; u < num_units; u += num_clusters) {
       const int qt = static_cast<int>(u % p.num_qt);
       const int64_t c = u / p.num_qt;
-      const int64_t t0 = c * p.tiles_per_chunk;
+      const int64_t t0 = p.tile_begin + c * p.tiles_per_chunk;
       const int64_t t1 = min(t0 + p.tiles_per_chunk, p.n_tiles);
       const int64_t qrow0 = (static_cast<int64_t>(qt) * CG + rank) * BLOCK_M + ew * 32;  // lane 0's query
       const int64_t qrow = qrow0 + lane;
@@ -218,30 +218,37 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] -= p.half_norm[min(cbase + j, n_rows - 1)];
           }
-          // four 8-wide group maxima (3-input max), then the chunk maximum: 18 instructions for 32 scores
-          float gm[4];
+          float m = fmax3(v[0], v[1], v[2]);
 #pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) {
-            const int b8 = g8 * 8;
-            gm[g8] = fmaxf(fmax3(fmax3(v[b8], v[b8 + 1], v[b8 + 2]), v[b8 + 3], v[b8 + 4]), fmax3(v[b8 + 5], v[b8 + 6], v[b8 + 7]));
-          }
-          const float m = fmaxf(fmax3(gm[0], gm[1], gm[2]), gm[3]);
-          const bool hit = m > tau;
-          if (__any_sync(kFullMask, hit)) {
-            if (hit) {
+          for (int j = 3; j < 31; j += 2) m = fmax3(m, v[j], v[j + 1]);
+          m = fmaxf(m, v[31]);
+          unsigned hm = __ballot_sync(kFullMask, m > tau);
+          if (hm) {
+            // Warp-cooperative append: a row with a survivor publishes its 32 scores through shared memory, then
+            // the 32 lanes test one column each and the survivors are written with one coalesced store.
+            float* stage = reinterpret_cast<float*>(my_hist);  // the prune histogram is idle here
+            do {
+              const int src = __ffs(hm) - 1;
+              hm &= hm - 1;
+              if (static_cast<int>(lane) == src) {
+                float4* d4 = reinterpret_cast<float4*>(stage);
 #pragma unroll
-              for (int g8 = 0; g8 < 4; ++g8) {
-                if (gm[g8] > tau) {
-#pragma unroll
-                  for (int j = g8 * 8; j < g8 * 8 + 8; ++j) {
-                    if (v[j] > tau && cbase + j < n_rows) {
-                      Entry e; e.score = v[j]; e.row = cbase + j;
-                      my_buf[cnt++] = e;
-                    }
-                  }
-                }
+                for (int j = 0; j < 8; ++j) d4[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
               }
-            }
+              __syncwarp();
+              const float sc = stage[lane];
+              const float tau_src = __shfl_sync(kFullMask, tau, src);
+              const int cnt_src = __shfl_sync(kFullMask, cnt, src);
+              const int32_t col = cbase + static_cast<int32_t>(lane);
+              const bool pass = sc > tau_src && col < n_rows;
+              const unsigned pm = __ballot_sync(kFullMask, pass);
+              if (pass) {
+                Entry e; e.score = sc; e.row = col;
+                (warp_buf0 + static_cast<int64_t>(src) * cap)[cnt_src + __popc(pm & lanemask_lt())] = e;
+              }
+              if (static_cast<int>(lane) == src) cnt += __popc(pm);
+              __syncwarp();
+            } while (hm);
             __syncwarp();
             unsigned need = __ballot_sync(kFullMask, cnt > cap - 32);
             while (need) {
