@@ -10,7 +10,8 @@ import os
 import threading
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libnexus_flat.so")
+# NEXUS_FLAT_LIB selects another build of the same C ABI (A/B timing of kernel variants on one box); default = in-tree build
+LIB_PATH = os.environ.get("NEXUS_FLAT_LIB") or os.path.join(HERE, "libnexus_flat.so")
 
 # enums (mirror include/nexus_flat.h)
 NXF_OK, NXF_EINVAL, NXF_ECUDA, NXF_ENOMEM, NXF_ENODEVICE, NXF_EUNSUPPORTED = 0, -1, -2, -3, -4, -5

@@ -411,9 +411,8 @@ struct SearchPlan {
   int grid = 0;
   int num_qt = 0, chunks = 1;
   int64_t tiles_per_chunk = 1, n_tiles = 0;
-  // K1 threshold-seeding pass over tiles [0, seed_tiles)
-  int64_t seed_tiles = 0, seed_tpc = 1;
-  int seed_chunks = 0, seed_grid = 0;
+  // K1 interleaved rounds
+  int round_tiles = 1, sync_window = 0;
   int64_t arena_stride = 0;
   int64_t owners = 0;
   // K2
@@ -494,23 +493,30 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       P.k_fetch = static_cast<int>(std::min<int64_t>(std::min<int64_t>(kf, NXF_MAX_K), idx->n));
       P.k_fetch = std::max(P.k_fetch, P.k_eff);
     }
-    P.n_tiles = ceil_div64(idx->n, 256);
-    P.num_qt = static_cast<int>(ceil_div64(nq, 128 * cg));
     const int clusters = idx->sm_count / cg;
-    // threshold seeding (DESIGN.md "seed pass"): search the first ~1/64 of the corpus, publish each query's exact
-    // k'-th best of that sample as its threshold, then run the main pass over the rest
-    if (P.n_tiles >= 128 && !env_int("NXF_K1_NO_SEED", 0)) {
-      P.seed_tiles = std::max<int64_t>(P.n_tiles / 64, std::min<int64_t>(P.n_tiles / 8, clusters));
-      plan_units(P.num_qt, P.seed_tiles, clusters, &P.seed_chunks, &P.seed_tpc);
-      P.seed_grid = static_cast<int>(std::min<int64_t>(clusters, static_cast<int64_t>(P.num_qt) * P.seed_chunks)) * cg;
+    // one launch serves at most one query tile per cluster (every cluster keeps <= 2 query tiles' state for the whole launch)
+    P.batch = std::min<int64_t>(nq, static_cast<int64_t>(clusters) * 128 * cg);
+    P.n_tiles = ceil_div64(idx->n, 256);
+    P.num_qt = static_cast<int>(ceil_div64(P.batch, 128 * cg));
+    const int64_t units = static_cast<int64_t>(P.num_qt) * P.n_tiles;
+    const int used = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(clusters, units)));
+    P.grid = used * cg;
+    // round = the corpus window all clusters share through L2: a multiple of used/gcd(used, num_qt) tiles makes the P pieces of
+    // a round exactly equal; sized to NXF_K1_ROUND_MB (default 32 MB)
+    {
+      int a = used, b = P.num_qt;
+      while (b) { const int t = a % b; a = b; b = t; }
+      const int64_t unit_tiles = used / a;
+      const int64_t tile_bytes = 256 * row_bytes;
+      const int64_t target = static_cast<int64_t>(std::max(1, env_int("NXF_K1_ROUND_MB", 32))) << 20;
+      const int64_t m = std::max<int64_t>(1, (target + unit_tiles * tile_bytes / 2) / (unit_tiles * tile_bytes));
+      P.round_tiles = static_cast<int>(std::min<int64_t>(unit_tiles * m, std::max<int64_t>(P.n_tiles, 1)));
+      P.sync_window = env_int("NXF_K1_SYNC_WINDOW", 1);
     }
-    plan_units(P.num_qt, P.n_tiles - P.seed_tiles, clusters, &P.chunks, &P.tiles_per_chunk);
-    const int64_t units = static_cast<int64_t>(P.num_qt) * P.chunks;
-    P.grid = static_cast<int>(std::min<int64_t>(clusters, units)) * cg;
+    P.chunks = static_cast<int>(ceil_div64(std::max<int64_t>(P.n_tiles, 1), P.round_tiles));  // reported as "chunks": rounds per launch
     P.cap = std::max(2 * P.k_fetch, P.k_fetch + 64);
-    P.owners = static_cast<int64_t>(std::max(P.grid, P.seed_grid)) * 128;
-    P.arena_stride = static_cast<int64_t>(P.chunks + P.seed_chunks) * P.k_fetch;
-    P.batch = nq;
+    P.owners = static_cast<int64_t>(P.grid) * 128 * 2;  // two query-tile slots per CTA
+    P.arena_stride = P.k_fetch;  // K1 folds every owner's candidates into ONE list of k' per query (merged under a lock)
   }
   return NXF_OK;
 }
@@ -557,6 +563,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     if (rc) return rc;
     if (idx->n == 0) break;
     if (P.path == NXF_PATH_STREAM) { batch = std::min<int64_t>(nq, P.batch); break; }
+    if (P.path == NXF_PATH_TENSOR && P.batch < batch) { batch = P.batch; continue; }  // re-plan for the per-launch query count
     const int64_t budget = (int64_t(6) << 30) << (it >= 6 ? 1 : 0);  // last tries: accept a larger arena
     const int64_t per_q = std::max<int64_t>(P.arena_stride * 8, 1);
     const int64_t gran = 128 * P.cta_group;
@@ -570,7 +577,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   // ---- carve scratch (two passes: size, then pointers) ----
   const size_t qsz = dtype_size(q_dtype);
   unsigned char* base = nullptr;
-  float* q_f32 = nullptr; void* q16 = nullptr; void* q_src = nullptr; uint32_t* tau_g = nullptr; uint32_t* qcnt = nullptr;
+  float* q_f32 = nullptr; void* q16 = nullptr; void* q_src = nullptr; uint32_t* tau_g = nullptr; uint32_t* qcnt = nullptr; uint32_t* qlock = nullptr;
   Entry* arena = nullptr; Entry* cand = nullptr; float* o_scores = nullptr; int64_t* o_ids = nullptr;
   const int64_t nq_pad = round_up64(batch, 256);
   for (int pass = 0; pass < 2; ++pass) {
@@ -578,8 +585,9 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     q_src = q_on_device ? nullptr : cv.take<unsigned char>(static_cast<size_t>(batch) * q_ld * qsz);
     q_f32 = cv.take<float>(static_cast<size_t>(nq_pad) * idx->ld);
     q16 = (P.path == NXF_PATH_TENSOR) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld) : nullptr;
-    tau_g = cv.take<uint32_t>(static_cast<size_t>(2 * nq_pad));
+    tau_g = cv.take<uint32_t>(static_cast<size_t>(3 * nq_pad + 64));  // tau | qcnt | lock | K1 round counter
     qcnt = tau_g ? tau_g + nq_pad : nullptr;
+    qlock = tau_g ? tau_g + 2 * nq_pad : nullptr;
     arena = cv.take<Entry>(static_cast<size_t>(batch) * P.arena_stride);
     cand = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(P.owners, 1)) * P.cap);
     if (!out_on_device) {
@@ -610,7 +618,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       if (rc) return rc;
       idx->stats.kernel_launches++;
     }
-    NXF_CUDA(cudaMemsetAsync(tau_g, 0, static_cast<size_t>(2 * nq_pad) * sizeof(uint32_t), stream));
+    NXF_CUDA(cudaMemsetAsync(tau_g, 0, static_cast<size_t>(3 * nq_pad + 64) * sizeof(uint32_t), stream));
 
     cudaEvent_t pe0 = nullptr, pe1 = nullptr;
     if (idx->profiling && P.path != NXF_PATH_NONE) {
@@ -619,7 +627,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       NXF_CUDA(cudaEventRecord(pe0, stream));
     }
     SinkParams sink;
-    sink.tau_g = tau_g; sink.qcnt = qcnt; sink.arena = arena; sink.cand = cand;
+    sink.tau_g = tau_g; sink.qcnt = qcnt; sink.lock = qlock; sink.arena = arena; sink.cand = cand;
     sink.arena_stride = P.arena_stride; sink.cap = P.cap; sink.k = P.k_fetch;
 
     if (P.path == NXF_PATH_STREAM) {
@@ -652,16 +660,17 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
       kp.sink = sink;
-      if (P.seed_tiles > 0) {
-        kp.tile_begin = 0; kp.n_tiles = P.seed_tiles; kp.chunks = P.seed_chunks; kp.tiles_per_chunk = P.seed_tpc;
-        rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, P.seed_grid, stream);
-        if (rc) return rc;
-        rc = launch_seed_tau(arena, qcnt, P.arena_stride, P.k_fetch, tau_g, bn, stream);
-        if (rc) return rc;
-        idx->stats.kernel_launches += 2;
+      kp.n_tiles = P.n_tiles; kp.round_tiles = P.round_tiles; kp.sync_window = P.sync_window;
+      kp.sync_ctr = tau_g + 3 * nq_pad;
+      // the last launch of a multi-batch search may hold fewer query tiles than planned: never more clusters than tile-units
+      int grid = P.grid;
+      {
+        const int64_t units = static_cast<int64_t>(kp.num_qt) * P.n_tiles;
+        if (units < grid / P.cta_group) grid = static_cast<int>(std::max<int64_t>(units, 1)) * P.cta_group;
       }
-      kp.tile_begin = P.seed_tiles; kp.n_tiles = P.n_tiles; kp.chunks = P.chunks; kp.tiles_per_chunk = P.tiles_per_chunk;
-      rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, P.grid, stream);
+      NXF_REQUIRE(kp.num_qt <= grid / P.cta_group || P.n_tiles == 0, "nxf_search: internal: %d query tiles for %d clusters", kp.num_qt,
+                  grid / P.cta_group);
+      rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
     }

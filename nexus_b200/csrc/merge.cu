@@ -234,34 +234,6 @@ int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, c
 }
 
 
-// ---- threshold seeding -------------------------------------------------------------------------
-// After the seed pass (the first ~1/64 of the corpus) every query's arena slice holds its candidates from
-// that sample.  The exact k_fetch-th best of the sample is a valid lower bound on the final k_fetch-th best,
-// and a far tighter one than any single owner's: publishing it in tau_g lets the main pass reject all but
-// ~k*ln(N/Ns) scores per query.
-__global__ void __launch_bounds__(mg::THREADS) seed_tau_kernel(const Entry* __restrict__ arena, const uint32_t* __restrict__ qcnt,
-                                                               int64_t arena_stride, int k_fetch, uint32_t* tau_g) {
-  __shared__ uint32_t hist[256];
-  __shared__ uint32_t sh_prefix;
-  __shared__ int sh_need;
-  const int64_t qi = blockIdx.x;
-  const Entry* __restrict__ src = arena + qi * arena_stride;
-  int64_t m64 = qcnt[qi];
-  if (m64 > arena_stride) m64 = arena_stride;
-  const int M = static_cast<int>(m64);
-  if (M < k_fetch) return;  // uniform per block
-  block_radix_select(M, k_fetch, [&](int i) { return okey(src[i].score); }, hist, &sh_prefix, &sh_need);
-  if (threadIdx.x == 0) atomicMax(&tau_g[qi], sh_prefix);
-}
-
-int launch_seed_tau(const Entry* arena, const uint32_t* qcnt, int64_t arena_stride, int k_fetch, uint32_t* tau_g, int64_t nq,
-                    cudaStream_t stream) {
-  if (nq <= 0) return NXF_OK;
-  seed_tau_kernel<<<static_cast<unsigned>(nq), mg::THREADS, 0, stream>>>(arena, qcnt, arena_stride, k_fetch, tau_g);
-  NXF_CUDA(cudaGetLastError());
-  return NXF_OK;
-}
-
 // ---- multi-list merge (multi-GPU shard merge) ---------------------------------------------------
 __global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(MergeListsParams p) {
   __shared__ uint64_t keys[mg::MAXK];

@@ -26,13 +26,14 @@ struct K1Params {
   int64_t n;    // corpus rows
   int64_t nq;   // query rows
   int kblocks;  // ld / 64
-  int num_qt;   // query tiles of 128*CG rows
-  int chunks;
-  int64_t tiles_per_chunk;
-  int64_t n_tiles;  // one past the last corpus tile of this launch (ceil(n / 256) for the main pass)
-  int64_t tile_begin;  // first corpus tile of this launch (the seed pass covers [0, T0), the main pass [T0, n_tiles))
+  int num_qt;   // query tiles of 128*CG rows (<= number of clusters)
+  int64_t n_tiles;     // ceil(n / 256)
+  int round_tiles;     // corpus tiles per round (the L2-resident window)
+  int sync_window;     // soft round barrier: a producer may run this many rounds ahead of the rest (0 = no barrier)
+  uint32_t* sync_ctr;  // [1] zeroed per launch: rounds completed, summed over clusters
   const float* half_norm;
-  int debug;  // bit0: epilogue skips the selection; bit1: epilogue skips the TMEM loads too (pipeline timing only)
+  int debug;  // timing experiments: bit0 epilogue skips the selection; bit1 also skips the TMEM loads; bit2 producer issues no TMA;
+              // bit3 issuer issues no MMA
   SinkParams sink;
 };
 
@@ -88,8 +89,6 @@ int launch_k2(int store_dtype, const K2Params& p, int nq_t, int rw, int grid, si
 size_t k2_smem_bytes(int64_t ld, int elem_size, int nq_t, int rw, int stages);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
-int launch_seed_tau(const Entry* arena, const uint32_t* qcnt, int64_t arena_stride, int k_fetch, uint32_t* tau_g, int64_t nq,
-                    cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,
                         cudaStream_t stream);
 int launch_half_norm(const void* rows, int dtype, int64_t ld, int64_t n, int dim, float* out, cudaStream_t stream);

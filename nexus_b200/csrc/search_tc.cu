@@ -18,8 +18,12 @@
 //           buffer (global memory, L2 resident); a buffer that could overflow is reduced to its exact
 //           top-k by the whole warp (radix select, select.cuh) and tau is raised to the k-th score,
 //           also published to tau_g[query] so every CTA working on the same query benefits.
-// Work decomposition: unit = (corpus chunk, query tile), query tile fastest: the CTAs running at any
-// moment share the corpus rows they stream (one HBM pass, L2 hits for the rest).
+// Work decomposition ("interleaved rounds"): the corpus is cut into rounds of R tiles sized to stay
+// L2-resident (tens of MB).  Inside a round the num_qt x R tile-units are laid on a line, query tile major, and cut
+// into P equal pieces, one per cluster -- so every cluster works on the SAME <= 2 query tiles for the whole launch
+// (their thresholds, counters and candidate buffers never move) while all clusters consume the same round of the
+// corpus at different offsets: each corpus tile comes from HBM once and from L2 for the other query tiles.  A soft
+// (timeout-guarded) round barrier between the producers keeps the clusters within one round of each other.
 #include "params.cuh"
 
 namespace nxf {
@@ -47,6 +51,106 @@ template <int CG> struct Cfg {
 };
 }  // namespace k1
 
+
+// ---------------------------------------------------------------------------------------------
+// epilogue helpers
+// ---------------------------------------------------------------------------------------------
+struct EpiState {
+  float tau;  // this row's running threshold (monotone)
+  int cnt;    // entries in this row's private candidate buffer
+};
+
+__device__ __forceinline__ uint32_t ld_cg_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ Entry ld_cg_entry(const Entry* p) {
+  uint32_t a, b;
+  asm volatile("ld.global.cg.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
+  Entry e;
+  e.score = __uint_as_float(a);
+  e.row = static_cast<int32_t>(b);
+  return e;
+}
+
+// One 32-column slice of the accumulator: this thread's row x 32 corpus rows [cbase, cbase+32).
+// Common case: 18 max ops, one vote, no branch taken.  A row whose slice maximum beats its threshold scans the
+// 8-column group(s) that did and appends the survivors to its PRIVATE buffer (no cross-lane work); a buffer that
+// could overflow on the next slice is reduced to its exact top-k by the whole warp and tau is raised.
+__device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbase, bool ragged, int32_t n_rows,
+                                          const float* __restrict__ half_norm, EpiState& st, Entry* __restrict__ my_buf,
+                                          Entry* __restrict__ warp_buf0, int cap, int k, uint32_t* my_hist, unsigned lane, bool valid,
+                                          uint32_t* tau_g, int64_t qrow) {
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
+  if (half_norm != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] -= half_norm[min(cbase + j, n_rows - 1)];
+  }
+  if (ragged) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (cbase + j >= n_rows) v[j] = -INFINITY;
+  }
+  float g[4];
+#pragma unroll
+  for (int q4 = 0; q4 < 4; ++q4) {
+    float a = fmax3(v[8 * q4], v[8 * q4 + 1], v[8 * q4 + 2]);
+    a = fmax3(a, v[8 * q4 + 3], v[8 * q4 + 4]);
+    a = fmax3(a, v[8 * q4 + 5], v[8 * q4 + 6]);
+    g[q4] = fmaxf(a, v[8 * q4 + 7]);
+  }
+  const float m = fmaxf(fmax3(g[0], g[1], g[2]), g[3]);
+  if (__any_sync(kFullMask, m > st.tau)) {
+    if (m > st.tau) {
+      const float tau = st.tau;
+      int cnt = st.cnt;
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        if (g[q4] > tau) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float sc = v[8 * q4 + j];
+            if (sc > tau) {
+              *reinterpret_cast<uint2*>(my_buf + cnt) = make_uint2(__float_as_uint(sc), static_cast<uint32_t>(cbase + 8 * q4 + j));
+              ++cnt;
+            }
+          }
+        }
+      }
+      st.cnt = cnt;
+    }
+    __syncwarp();
+    unsigned need = __ballot_sync(kFullMask, st.cnt > cap - 32);
+    while (need) {
+      const int src = __ffs(need) - 1;
+      need &= need - 1;
+      const int n_src = __shfl_sync(kFullMask, st.cnt, src);
+      const uint32_t kth = warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
+      if (static_cast<int>(lane) == src) {
+        st.cnt = k;
+        st.tau = fmaxf(st.tau, okey_inv(kth));
+        if (valid) atomicMax(&tau_g[qrow], kth);
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// Round schedule shared by the three warp roles.  Line positions [a, b) of cluster j in a round of R tiles cover
+// query tiles qt = pos / R at corpus offsets pos % R.
+struct RoundPiece {
+  int64_t R, a, b;
+};
+__device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0, int64_t cluster_id, int64_t num_clusters) {
+  RoundPiece rp;
+  rp.R = min(static_cast<int64_t>(p.round_tiles), p.n_tiles - r0);
+  rp.a = cluster_id * p.num_qt * rp.R / num_clusters;
+  rp.b = (cluster_id + 1) * p.num_qt * rp.R / num_clusters;
+  return rp;
+}
+
 template <int CG, bool BF16>
 __global__ void __launch_bounds__(k1::THREADS, 1)
 k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K1Params p) {
@@ -66,7 +170,6 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
   const int64_t cluster_id = blockIdx.x / CG;
   const int64_t num_clusters = gridDim.x / CG;
-  const int64_t num_units = static_cast<int64_t>(p.num_qt) * p.chunks;
 
   if (CG == 2) cluster_sync_all();  // both CTAs of the pair are resident before cta_group::2 alloc
   if (warp == 0 && lane == 0) {
@@ -92,29 +195,41 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int64_t u = cluster_id; u < num_units; u += num_clusters) {
-        const int qt = static_cast<int>(u % p.num_qt);
-        const int64_t c = u / p.num_qt;
-        const int64_t t0 = p.tile_begin + c * p.tiles_per_chunk;
-        const int64_t t1 = min(t0 + p.tiles_per_chunk, p.n_tiles);
-        const int32_t q_row0 = static_cast<int32_t>((static_cast<int64_t>(qt) * CG + rank) * BLOCK_M);
-        for (int64_t t = t0; t < t1; ++t) {
-          const int32_t c_row0 = static_cast<int32_t>(t * BLOCK_N + rank * C::LOAD_N);
-          for (int kb = 0; kb < p.kblocks; ++kb) {
-            mbar_wait(&empty[s], ph ^ 1);
-            if (CG == 1) {
-              mbar_expect_tx(&full[s], C::STAGE_BYTES);
-              tma_load_2d(&tmap_q, &full[s], a_ptr(s), kb * BLOCK_K, q_row0, kEvictLast);
-              tma_load_2d(&tmap_c, &full[s], b_ptr(s), kb * BLOCK_K, c_row0, kEvictNormal);
-            } else {
-              tma_load_2d_2sm(&tmap_q, &full[s], a_ptr(s), kb * BLOCK_K, q_row0, kEvictLast);
-              tma_load_2d_2sm(&tmap_c, &full[s], b_ptr(s), kb * BLOCK_K, c_row0, kEvictNormal);
-              if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
-              else mbar_arrive_cluster(&full[s], 0);
-            }
-            if (++s == C::STAGES) { s = 0; ph ^= 1; }
-          }
+      int64_t ri = 0;
+      for (int64_t r0 = 0; r0 < p.n_tiles; r0 += p.round_tiles, ++ri) {
+        if (p.sync_window > 0 && rank == 0 && ri >= p.sync_window) {
+          // soft round barrier: wait until (on average) every cluster finished issuing round ri - window; bounded spin, so a
+          // cluster that is not resident (foreign kernels on some SMs) costs lockstep, never progress
+          const uint32_t want = static_cast<uint32_t>(num_clusters * (ri - p.sync_window + 1));
+          for (int spin = 0; spin < 20000 && ld_acquire_u32(p.sync_ctr) < want; ++spin) __nanosleep(100);
         }
+        const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
+        for (int64_t pos = rp.a; pos < rp.b;) {
+          const int64_t qt = pos / rp.R;
+          const int64_t lo = pos - qt * rp.R, hi = min(rp.b - qt * rp.R, rp.R);
+          const int32_t q_row0 = static_cast<int32_t>((qt * CG + rank) * BLOCK_M);
+          for (int64_t t = r0 + lo; t < r0 + hi; ++t) {
+            const int32_t c_row0 = static_cast<int32_t>(t * BLOCK_N + rank * C::LOAD_N);
+            for (int kb = 0; kb < p.kblocks; ++kb) {
+              mbar_wait(&empty[s], ph ^ 1);
+              if (p.debug & 4) {  // pipeline timing only: no loads, the MMAs run on whatever the ring holds
+                if (CG == 1 || rank == 0) mbar_arrive(&full[s]); else mbar_arrive_cluster(&full[s], 0);
+              } else if (CG == 1) {
+                mbar_expect_tx(&full[s], C::STAGE_BYTES);
+                tma_load_2d(&tmap_q, &full[s], a_ptr(s), kb * BLOCK_K, q_row0, kEvictLast);
+                tma_load_2d(&tmap_c, &full[s], b_ptr(s), kb * BLOCK_K, c_row0, kEvictNormal);
+              } else {
+                tma_load_2d_2sm(&tmap_q, &full[s], a_ptr(s), kb * BLOCK_K, q_row0, kEvictLast);
+                tma_load_2d_2sm(&tmap_c, &full[s], b_ptr(s), kb * BLOCK_K, c_row0, kEvictNormal);
+                if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
+                else mbar_arrive_cluster(&full[s], 0);
+              }
+              if (++s == C::STAGES) { s = 0; ph ^= 1; }
+            }
+          }
+          pos = qt * rp.R + hi;
+        }
+        if (p.sync_window > 0 && rank == 0) red_release_add_u32(p.sync_ctr, 1u);
       }
     }
     __syncwarp();
@@ -125,11 +240,9 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       int s = 0;
       uint32_t ph = 0;
       uint32_t iter = 0;
-      for (int64_t u = cluster_id; u < num_units; u += num_clusters) {
-        const int64_t c = u / p.num_qt;
-        const int64_t t0 = p.tile_begin + c * p.tiles_per_chunk;
-        const int64_t t1 = min(t0 + p.tiles_per_chunk, p.n_tiles);
-        for (int64_t t = t0; t < t1; ++t, ++iter) {
+      for (int64_t r0 = 0; r0 < p.n_tiles; r0 += p.round_tiles) {
+        const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
+        for (int64_t i = rp.a; i < rp.b; ++i, ++iter) {  // one accumulator tile per line position, whatever its query tile
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
           mbar_wait(&tempty[as], aph ^ 1);
           tc_fence_after();
@@ -139,10 +252,12 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             tc_fence_after();
             const uint64_t a_desc = umma_desc_sw128(smem_u32(a_ptr(s)));
             const uint64_t b_desc = umma_desc_sw128(smem_u32(b_ptr(s)));
+            if (!(p.debug & 8)) {
 #pragma unroll
-            for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) {
-              // advance 16 elements = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
-              umma_f16<CG>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, (kb | k4) != 0 ? 1u : 0u);
+              for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) {
+                // advance 16 elements = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
+                umma_f16<CG>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, (kb | k4) != 0 ? 1u : 0u);
+              }
             }
             umma_commit<CG>(&empty[s]);  // smem stage reusable once these MMAs retire
             if (++s == C::STAGES) { s = 0; ph ^= 1; }
@@ -168,134 +283,117 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint32_t* my_hist = hist + ew * 256;
     const int cap = p.sink.cap;
     const int k = p.sink.k;
-    Entry* warp_buf0 = p.sink.cand + (static_cast<int64_t>(blockIdx.x) * BLOCK_M + ew * 32) * cap;  // lane 0's buffer
-    Entry* my_buf = warp_buf0 + static_cast<int64_t>(lane) * cap;
     const int32_t n_rows = static_cast<int32_t>(p.n);
+    // this cluster's (at most two) query tiles: slot 0 = qt_base, slot 1 = qt_base + 1
+    const int64_t qt_base = cluster_id * p.num_qt / num_clusters;
+    auto slot_buf0 = [&](int slot) {  // lane 0's candidate buffer of this warp for that slot
+      return p.sink.cand + ((static_cast<int64_t>(blockIdx.x) * 2 + slot) * BLOCK_M + ew * 32) * cap;
+    };
+    auto slot_qrow0 = [&](int slot) { return ((qt_base + slot) * CG + rank) * BLOCK_M + ew * 32; };
+    auto slot_valid = [&](int slot) { return qt_base + slot < p.num_qt && slot_qrow0(slot) + lane < p.nq; };
+    EpiState cur, alt;  // per-row state of the active slot / the other slot (swapped when the piece crosses a query tile)
+    cur.cnt = 0; alt.cnt = 0;
+    cur.tau = slot_valid(0) ? tau_load(p.sink.tau_g, slot_qrow0(0) + lane) : INFINITY;  // padded rows accept nothing
+    alt.tau = slot_valid(1) ? tau_load(p.sink.tau_g, slot_qrow0(1) + lane) : INFINITY;
+    int cur_slot = 0;
     uint32_t iter = 0;
 
-    for (int64_t u = cluster_id; u < num_units; u += num_clusters) {
-      const int qt = static_cast<int>(u % p.num_qt);
-      const int64_t c = u / p.num_qt;
-      const int64_t t0 = p.tile_begin + c * p.tiles_per_chunk;
-      const int64_t t1 = min(t0 + p.tiles_per_chunk, p.n_tiles);
-      const int64_t qrow0 = (static_cast<int64_t>(qt) * CG + rank) * BLOCK_M + ew * 32;  // lane 0's query
-      const int64_t qrow = qrow0 + lane;
-      const bool valid = qrow < p.nq;
-      float tau = valid ? tau_load(p.sink.tau_g, qrow) : INFINITY;  // padded rows accept nothing
-      int cnt = 0;
-      float tau_next = tau;
-
-      for (int64_t t = t0; t < t1; ++t, ++iter) {
-        const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
-        tau = fmaxf(tau, tau_next);  // other CTAs' progress on this query (loaded during the previous tile)
-        mbar_wait(&tfull[as], aph);
-        tc_fence_after();
-        const int32_t col0 = static_cast<int32_t>(t * BLOCK_N);
-#pragma unroll 1
-        for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
-          uint32_t vr[32];
-          if (!(p.debug & 2)) {
-            tmem_ld32(taddr + as * BLOCK_N + ch * 32, vr);
-            tmem_ld_wait();
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) vr[j] = 0;
-          }
-          if (ch == BLOCK_N / 32 - 1) {
-            // accumulator fully read: hand the TMEM buffer back to the MMA issuer
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-              if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]);
-            }
-          }
-          if (p.debug & 1) continue;
-          float v[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
-          const int32_t cbase = col0 + ch * 32;
-          if (p.half_norm != nullptr) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] -= p.half_norm[min(cbase + j, n_rows - 1)];
-          }
-          float m = fmax3(v[0], v[1], v[2]);
-#pragma unroll
-          for (int j = 3; j < 31; j += 2) m = fmax3(m, v[j], v[j + 1]);
-          m = fmaxf(m, v[31]);
-          unsigned hm = __ballot_sync(kFullMask, m > tau);
-          if (hm) {
-            // Warp-cooperative append: a row with a survivor publishes its 32 scores through shared memory, then
-            // the 32 lanes test one column each and the survivors are written with one coalesced store.
-            float* stage = reinterpret_cast<float*>(my_hist);  // the prune histogram is idle here
-            do {
-              const int src = __ffs(hm) - 1;
-              hm &= hm - 1;
-              if (static_cast<int>(lane) == src) {
-                float4* d4 = reinterpret_cast<float4*>(stage);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) d4[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-              }
-              __syncwarp();
-              const float sc = stage[lane];
-              const float tau_src = __shfl_sync(kFullMask, tau, src);
-              const int cnt_src = __shfl_sync(kFullMask, cnt, src);
-              const int32_t col = cbase + static_cast<int32_t>(lane);
-              const bool pass = sc > tau_src && col < n_rows;
-              const unsigned pm = __ballot_sync(kFullMask, pass);
-              if (pass) {
-                Entry e; e.score = sc; e.row = col;
-                (warp_buf0 + static_cast<int64_t>(src) * cap)[cnt_src + __popc(pm & lanemask_lt())] = e;
-              }
-              if (static_cast<int>(lane) == src) cnt += __popc(pm);
-              __syncwarp();
-            } while (hm);
-            __syncwarp();
-            unsigned need = __ballot_sync(kFullMask, cnt > cap - 32);
-            while (need) {
-              const int src = __ffs(need) - 1;
-              need &= need - 1;
-              const int n_src = __shfl_sync(kFullMask, cnt, src);
-              const uint32_t kth = warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
-              if (static_cast<int>(lane) == src) {
-                cnt = k;
-                tau = fmaxf(tau, okey_inv(kth));
-                if (valid) atomicMax(&p.sink.tau_g[qrow], kth);
-              }
-              __syncwarp();
-            }
-          }
+    for (int64_t r0 = 0; r0 < p.n_tiles; r0 += p.round_tiles) {
+      const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
+      for (int64_t pos = rp.a; pos < rp.b;) {
+        const int64_t qt = pos / rp.R;
+        const int64_t lo = pos - qt * rp.R, hi = min(rp.b - qt * rp.R, rp.R);
+        pos = qt * rp.R + hi;
+        const int slot = static_cast<int>(qt - qt_base);
+        if (slot != cur_slot) {
+          const EpiState tmp = cur; cur = alt; alt = tmp;
+          cur_slot = slot;
         }
-        if (valid) tau_next = tau_load(p.sink.tau_g, qrow);
-      }
+        Entry* warp_buf0 = slot_buf0(slot);
+        Entry* my_buf = warp_buf0 + static_cast<int64_t>(lane) * cap;
+        const int64_t qrow = slot_qrow0(slot) + lane;
+        const bool valid = qrow < p.nq;
+        float tau_next = valid ? tau_load(p.sink.tau_g, qrow) : cur.tau;
 
-      // ---- unit end: prune to k, publish, flush the 32 rows of this warp to the arena ----
-      __syncwarp();
-      unsigned over = __ballot_sync(kFullMask, cnt > k);
-      while (over) {
-        const int src = __ffs(over) - 1;
-        over &= over - 1;
-        const int n_src = __shfl_sync(kFullMask, cnt, src);
-        const uint32_t kth = warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
-        if (static_cast<int>(lane) == src) {
-          cnt = k;
-          if (valid) atomicMax(&p.sink.tau_g[qrow], kth);
+        for (int64_t t = r0 + lo; t < r0 + hi; ++t, ++iter) {
+          const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
+          cur.tau = fmaxf(cur.tau, tau_next);  // other owners' progress on this query (loaded during the previous tile)
+          mbar_wait(&tfull[as], aph);
+          tc_fence_after();
+          const int32_t col0 = static_cast<int32_t>(t * BLOCK_N);
+          const bool ragged = col0 + BLOCK_N > n_rows;  // only the last corpus tile: rows past n are TMA zero fill
+          const uint32_t tbase = taddr + as * BLOCK_N;
+#pragma unroll 1
+          for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+            uint32_t vr[32];
+            if (!(p.debug & 2)) {
+              tmem_ld32(tbase + ch * 32, vr);
+              tmem_ld_wait_dep(vr);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) vr[j] = 0;
+            }
+            if (ch == BLOCK_N / 32 - 1) {
+              // accumulator fully read: hand the TMEM buffer back to the MMA issuer
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]); }
+            }
+            if (p.debug & 1) continue;
+            epi_chunk(vr, col0 + ch * 32, ragged, n_rows, p.half_norm, cur, my_buf, warp_buf0, cap, k, my_hist, lane, valid,
+                      p.sink.tau_g, qrow);
+          }
+          if (valid) tau_next = tau_load(p.sink.tau_g, qrow);
+        }
+      }
+    }
+
+    // ---- end of the launch: fold both slots' rows into the per-query global top-k' lists ----
+    __syncwarp();
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+      if (qt_base + slot >= p.num_qt) break;
+      const int my_cnt = (slot == cur_slot) ? cur.cnt : alt.cnt;
+      Entry* warp_buf0 = slot_buf0(slot);
+      const int64_t qrow0 = slot_qrow0(slot);
+#pragma unroll 1
+      for (int src = 0; src < 32; ++src) {
+        const int64_t q = qrow0 + src;
+        if (q >= p.nq) break;  // uniform
+        int n = __shfl_sync(kFullMask, my_cnt, src);
+        if (n == 0) continue;  // uniform
+        Entry* buf = warp_buf0 + static_cast<int64_t>(src) * cap;
+        // per-query lock: the list is read-modify-written once by each of the (<= 4) owners of the query
+        if (lane == 0) {
+          while (atomicCAS(&p.sink.lock[q], 0u, 1u) != 0u) __nanosleep(100);
+          __threadfence();
+        }
+        __syncwarp();
+        const int m = static_cast<int>(ld_cg_u32(&p.sink.qcnt[q]));
+        if (n + m > cap) {  // own candidates do not leave room for the list: reduce them to k first
+          warp_prune(buf, n, k, my_hist);
+          n = k;
+          __syncwarp();
+        }
+        Entry* gl = p.sink.arena + q * p.sink.arena_stride;
+        for (int i = lane; i < m; i += 32) buf[n + i] = ld_cg_entry(gl + i);
+        __syncwarp();
+        int tot = n + m;
+        if (tot > k) {
+          warp_prune(buf, tot, k, my_hist);
+          tot = k;
+          __syncwarp();
+        }
+        for (int i = lane; i < tot; i += 32) gl[i] = buf[i];
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+          *reinterpret_cast<volatile uint32_t*>(&p.sink.qcnt[q]) = static_cast<uint32_t>(tot);
+          __threadfence();
+          atomicExch(&p.sink.lock[q], 0u);
         }
         __syncwarp();
       }
-      if (!valid) cnt = 0;
-      uint32_t pos = 0;
-      if (cnt > 0) pos = atomicAdd(&p.sink.qcnt[qrow], static_cast<uint32_t>(cnt));
-      if (static_cast<int64_t>(pos) + cnt > p.sink.arena_stride) cnt = 0;  // cannot happen by construction
-      __syncwarp();
-#pragma unroll 4
-      for (int src = 0; src < 32; ++src) {
-        const int n_src = __shfl_sync(kFullMask, cnt, src);
-        const uint32_t pos_src = __shfl_sync(kFullMask, pos, src);
-        const Entry* from = warp_buf0 + static_cast<int64_t>(src) * cap;
-        Entry* to = p.sink.arena + (qrow0 + src) * p.sink.arena_stride + pos_src;
-        for (int i = lane; i < n_src; i += 32) to[i] = from[i];
-      }
-      __syncwarp();
     }
   }
 
