@@ -514,7 +514,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       P.sync_window = env_int("NXF_K1_SYNC_WINDOW", 1);
     }
     P.chunks = static_cast<int>(ceil_div64(std::max<int64_t>(P.n_tiles, 1), P.round_tiles));  // reported as "chunks": rounds per launch
-    P.cap = std::max(2 * P.k_fetch, P.k_fetch + 64);
+    P.cap = 2 * P.k_fetch + 256;  // pruned between tiles once fewer than 256 (one tile of appends) slots are left
     P.owners = static_cast<int64_t>(P.grid) * 128 * 2;  // two query-tile slots per CTA
     P.arena_stride = P.k_fetch;  // K1 folds every owner's candidates into ONE list of k' per query (merged under a lock)
   }

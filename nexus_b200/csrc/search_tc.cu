@@ -75,13 +75,11 @@ __device__ __forceinline__ Entry ld_cg_entry(const Entry* p) {
 }
 
 // One 32-column slice of the accumulator: this thread's row x 32 corpus rows [cbase, cbase+32).
-// Common case: 18 max ops, one vote, no branch taken.  A row whose slice maximum beats its threshold scans the
-// 8-column group(s) that did and appends the survivors to its PRIVATE buffer (no cross-lane work); a buffer that
-// could overflow on the next slice is reduced to its exact top-k by the whole warp and tau is raised.
+// Common case: 18 max ops and one branch not taken.  A row whose slice maximum beats its threshold scans the
+// 8-column group(s) that did and appends the survivors to its PRIVATE buffer (no cross-lane work, bounded time: the
+// accumulator is held while this runs).  Buffers are pruned between tiles (phase B in the kernel), never here.
 __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbase, bool ragged, int32_t n_rows,
-                                          const float* __restrict__ half_norm, EpiState& st, Entry* __restrict__ my_buf,
-                                          Entry* __restrict__ warp_buf0, int cap, int k, uint32_t* my_hist, unsigned lane, bool valid,
-                                          uint32_t* tau_g, int64_t qrow) {
+                                          const float* __restrict__ half_norm, EpiState& st, Entry* __restrict__ my_buf) {
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
@@ -102,39 +100,23 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbas
     g[q4] = fmaxf(a, v[8 * q4 + 7]);
   }
   const float m = fmaxf(fmax3(g[0], g[1], g[2]), g[3]);
-  if (__any_sync(kFullMask, m > st.tau)) {
-    if (m > st.tau) {
-      const float tau = st.tau;
-      int cnt = st.cnt;
+  if (m > st.tau) {
+    const float tau = st.tau;
+    int cnt = st.cnt;
 #pragma unroll
-      for (int q4 = 0; q4 < 4; ++q4) {
-        if (g[q4] > tau) {
+    for (int q4 = 0; q4 < 4; ++q4) {
+      if (g[q4] > tau) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float sc = v[8 * q4 + j];
-            if (sc > tau) {
-              *reinterpret_cast<uint2*>(my_buf + cnt) = make_uint2(__float_as_uint(sc), static_cast<uint32_t>(cbase + 8 * q4 + j));
-              ++cnt;
-            }
+        for (int j = 0; j < 8; ++j) {
+          const float sc = v[8 * q4 + j];
+          if (sc > tau) {
+            *reinterpret_cast<uint2*>(my_buf + cnt) = make_uint2(__float_as_uint(sc), static_cast<uint32_t>(cbase + 8 * q4 + j));
+            ++cnt;
           }
         }
       }
-      st.cnt = cnt;
     }
-    __syncwarp();
-    unsigned need = __ballot_sync(kFullMask, st.cnt > cap - 32);
-    while (need) {
-      const int src = __ffs(need) - 1;
-      need &= need - 1;
-      const int n_src = __shfl_sync(kFullMask, st.cnt, src);
-      const uint32_t kth = warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
-      if (static_cast<int>(lane) == src) {
-        st.cnt = k;
-        st.tau = fmaxf(st.tau, okey_inv(kth));
-        if (valid) atomicMax(&tau_g[qrow], kth);
-      }
-      __syncwarp();
-    }
+    st.cnt = cnt;
   }
 }
 
@@ -317,31 +299,57 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
         for (int64_t t = r0 + lo; t < r0 + hi; ++t, ++iter) {
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
-          cur.tau = fmaxf(cur.tau, tau_next);  // other owners' progress on this query (loaded during the previous tile)
           mbar_wait(&tfull[as], aph);
           tc_fence_after();
           const int32_t col0 = static_cast<int32_t>(t * BLOCK_N);
           const bool ragged = col0 + BLOCK_N > n_rows;  // only the last corpus tile: rows past n are TMA zero fill
           const uint32_t tbase = taddr + as * BLOCK_N;
+          if (p.debug & 2) {
+            // pipeline timing only: hand the accumulator back without reading it
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]); }
+            continue;
+          }
+          // Phase A (holds the accumulator): two register buffers, the tcgen05.ld of slice ch+1 is in flight while slice
+          // ch is filtered
+          uint32_t va[32], vb[32];
+          tmem_ld32(tbase, va);
 #pragma unroll 1
-          for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
-            uint32_t vr[32];
-            if (!(p.debug & 2)) {
-              tmem_ld32(tbase + ch * 32, vr);
-              tmem_ld_wait_dep(vr);
+          for (int ch = 0; ch < BLOCK_N / 32; ch += 2) {
+            tmem_ld_wait_dep(va);
+            tmem_ld32(tbase + (ch + 1) * 32, vb);
+            if (!(p.debug & 1)) epi_chunk(va, col0 + ch * 32, ragged, n_rows, p.half_norm, cur, my_buf);
+            tmem_ld_wait_dep(vb);
+            if (ch + 2 < BLOCK_N / 32) {
+              tmem_ld32(tbase + (ch + 2) * 32, va);
             } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) vr[j] = 0;
-            }
-            if (ch == BLOCK_N / 32 - 1) {
               // accumulator fully read: hand the TMEM buffer back to the MMA issuer
               tc_fence_before();
               __syncwarp();
               if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]); }
             }
-            if (p.debug & 1) continue;
-            epi_chunk(vr, col0 + ch * 32, ragged, n_rows, p.half_norm, cur, my_buf, warp_buf0, cap, k, my_hist, lane, valid,
-                      p.sink.tau_g, qrow);
+            if (!(p.debug & 1)) epi_chunk(vb, col0 + (ch + 1) * 32, ragged, n_rows, p.half_norm, cur, my_buf);
+          }
+          // other owners' progress on this query: loaded during the previous tile, folded in only now so that its latency
+          // hides behind phase A
+          cur.tau = fmaxf(cur.tau, tau_next);
+          // Phase B (the accumulator is already back with the MMA issuer): rows whose buffer could overflow during the next
+          // tile (<= 256 appends) are reduced to their exact top-k' by the whole warp; tau rises to the k'-th score and is
+          // published for the other owners of the query
+          __syncwarp();  // this tile's appends (thread-private global stores) are visible to the warp
+          unsigned need = __ballot_sync(kFullMask, cur.cnt > cap - BLOCK_N);
+          while (need) {
+            const int src = __ffs(need) - 1;
+            need &= need - 1;
+            const int n_src = __shfl_sync(kFullMask, cur.cnt, src);
+            const uint32_t kth = warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
+            if (static_cast<int>(lane) == src) {
+              cur.cnt = k;
+              cur.tau = fmaxf(cur.tau, okey_inv(kth));
+              if (valid) atomicMax(&p.sink.tau_g[qrow], kth);
+            }
+            __syncwarp();
           }
           if (valid) tau_next = tau_load(p.sink.tau_g, qrow);
         }
