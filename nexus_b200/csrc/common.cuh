@@ -272,13 +272,14 @@ __host__ __device__ constexpr uint32_t umma_idesc_f16(bool bf16, int m, int n) {
          (static_cast<uint32_t>(m >> 4) << 24);
 }
 
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+// relaxed on purpose: an acquire load compiles to LDG.STRONG + CCTL.IVALL (whole-L1 invalidate) and this is only a pacing hint
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
   uint32_t v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void red_release_add_u32(uint32_t* p, uint32_t v) {
-  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void red_relaxed_add_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 __device__ __forceinline__ float fmax3(float a, float b, float c) {

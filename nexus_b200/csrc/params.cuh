@@ -33,7 +33,7 @@ struct K1Params {
   uint32_t* sync_ctr;  // [1] zeroed per launch: rounds completed, summed over clusters
   const float* half_norm;
   int debug;  // timing experiments: bit0 epilogue skips the selection; bit1 also skips the TMEM loads; bit2 producer issues no TMA;
-              // bit3 issuer issues no MMA
+              // bit3 issuer issues no MMA; bit4 epilogue computes the maxima but never appends
   SinkParams sink;
 };
 

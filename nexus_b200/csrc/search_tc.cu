@@ -78,16 +78,20 @@ __device__ __forceinline__ Entry ld_cg_entry(const Entry* p) {
 // Common case: 18 max ops and one branch not taken.  A row whose slice maximum beats its threshold scans the
 // 8-column group(s) that did and appends the survivors to its PRIVATE buffer (no cross-lane work, bounded time: the
 // accumulator is held while this runs).  Buffers are pruned between tiles (phase B in the kernel), never here.
-__device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbase, bool ragged, int32_t n_rows,
-                                          const float* __restrict__ half_norm, EpiState& st, Entry* __restrict__ my_buf) {
+// ADJ = false is the hot instantiation: the accumulator registers are used in place (no copies).  ADJ = true (L2 metric
+// or the ragged last corpus tile) first subtracts 0.5*|c|^2 and masks the rows past the end of the corpus.
+template <bool ADJ>
+__device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbase, int32_t n_rows,
+                                          const float* __restrict__ half_norm, EpiState& st, uint32_t* __restrict__ cand_words,
+                                          uint32_t my_first, int debug) {
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
-  if (half_norm != nullptr) {
+  if (ADJ) {
+    if (half_norm != nullptr) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] -= half_norm[min(cbase + j, n_rows - 1)];
-  }
-  if (ragged) {
+      for (int j = 0; j < 32; ++j) v[j] -= half_norm[min(cbase + j, n_rows - 1)];
+    }
 #pragma unroll
     for (int j = 0; j < 32; ++j) if (cbase + j >= n_rows) v[j] = -INFINITY;
   }
@@ -100,9 +104,11 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbas
     g[q4] = fmaxf(a, v[8 * q4 + 7]);
   }
   const float m = fmaxf(fmax3(g[0], g[1], g[2]), g[3]);
-  if (m > st.tau) {
+  if (m > st.tau && !(debug & 16)) {
     const float tau = st.tau;
-    int cnt = st.cnt;
+    // entry index in the candidate arena (uniform base + 32-bit index: one IMAD.WIDE per address); score and row go out
+    // as two 32-bit stores so that no register pairing is forced on the accumulator values of the common path
+    uint32_t w = my_first + static_cast<uint32_t>(st.cnt);
 #pragma unroll
     for (int q4 = 0; q4 < 4; ++q4) {
       if (g[q4] > tau) {
@@ -110,13 +116,14 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbas
         for (int j = 0; j < 8; ++j) {
           const float sc = v[8 * q4 + j];
           if (sc > tau) {
-            *reinterpret_cast<uint2*>(my_buf + cnt) = make_uint2(__float_as_uint(sc), static_cast<uint32_t>(cbase + 8 * q4 + j));
-            ++cnt;
+            cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(sc);
+            cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(cbase + 8 * q4 + j);
+            ++w;
           }
         }
       }
     }
-    st.cnt = cnt;
+    st.cnt = static_cast<int>(w - my_first);
   }
 }
 
@@ -183,7 +190,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           // soft round barrier: wait until (on average) every cluster finished issuing round ri - window; bounded spin, so a
           // cluster that is not resident (foreign kernels on some SMs) costs lockstep, never progress
           const uint32_t want = static_cast<uint32_t>(num_clusters * (ri - p.sync_window + 1));
-          for (int spin = 0; spin < 20000 && ld_acquire_u32(p.sync_ctr) < want; ++spin) __nanosleep(100);
+          for (int spin = 0; spin < 20000 && ld_relaxed_u32(p.sync_ctr) < want; ++spin) __nanosleep(100);
         }
         const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
         for (int64_t pos = rp.a; pos < rp.b;) {
@@ -211,7 +218,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           }
           pos = qt * rp.R + hi;
         }
-        if (p.sync_window > 0 && rank == 0) red_release_add_u32(p.sync_ctr, 1u);
+        if (p.sync_window > 0 && rank == 0) red_relaxed_add_u32(p.sync_ctr, 1u);
       }
     }
     __syncwarp();
@@ -266,6 +273,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const int cap = p.sink.cap;
     const int k = p.sink.k;
     const int32_t n_rows = static_cast<int32_t>(p.n);
+    uint32_t* cand_words = reinterpret_cast<uint32_t*>(p.sink.cand);
     // this cluster's (at most two) query tiles: slot 0 = qt_base, slot 1 = qt_base + 1
     const int64_t qt_base = cluster_id * p.num_qt / num_clusters;
     auto slot_buf0 = [&](int slot) {  // lane 0's candidate buffer of this warp for that slot
@@ -292,7 +300,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           cur_slot = slot;
         }
         Entry* warp_buf0 = slot_buf0(slot);
-        Entry* my_buf = warp_buf0 + static_cast<int64_t>(lane) * cap;
+        const uint32_t my_first = static_cast<uint32_t>((warp_buf0 - p.sink.cand) + static_cast<int64_t>(lane) * cap);
         const int64_t qrow = slot_qrow0(slot) + lane;
         const bool valid = qrow < p.nq;
         float tau_next = valid ? tau_load(p.sink.tau_g, qrow) : cur.tau;
@@ -302,7 +310,8 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           mbar_wait(&tfull[as], aph);
           tc_fence_after();
           const int32_t col0 = static_cast<int32_t>(t * BLOCK_N);
-          const bool ragged = col0 + BLOCK_N > n_rows;  // only the last corpus tile: rows past n are TMA zero fill
+          // slow-path epilogue: the last corpus tile (rows past n are TMA zero fill) or the L2 metric
+          const bool adj = (col0 + BLOCK_N > n_rows) || (p.half_norm != nullptr);
           const uint32_t tbase = taddr + as * BLOCK_N;
           if (p.debug & 2) {
             // pipeline timing only: hand the accumulator back without reading it
@@ -319,7 +328,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           for (int ch = 0; ch < BLOCK_N / 32; ch += 2) {
             tmem_ld_wait_dep(va);
             tmem_ld32(tbase + (ch + 1) * 32, vb);
-            if (!(p.debug & 1)) epi_chunk(va, col0 + ch * 32, ragged, n_rows, p.half_norm, cur, my_buf);
+            if (!(p.debug & 1)) {
+              if (adj) epi_chunk<true>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
+              else epi_chunk<false>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
+            }
             tmem_ld_wait_dep(vb);
             if (ch + 2 < BLOCK_N / 32) {
               tmem_ld32(tbase + (ch + 2) * 32, va);
@@ -329,7 +341,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               __syncwarp();
               if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]); }
             }
-            if (!(p.debug & 1)) epi_chunk(vb, col0 + (ch + 1) * 32, ragged, n_rows, p.half_norm, cur, my_buf);
+            if (!(p.debug & 1)) {
+              if (adj) epi_chunk<true>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
+              else epi_chunk<false>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
+            }
           }
           // other owners' progress on this query: loaded during the previous tile, folded in only now so that its latency
           // hides behind phase A
