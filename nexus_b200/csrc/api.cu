@@ -512,6 +512,11 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       const int64_t m = std::max<int64_t>(1, (target + unit_tiles * tile_bytes / 2) / (unit_tiles * tile_bytes));
       P.round_tiles = static_cast<int>(std::min<int64_t>(unit_tiles * m, std::max<int64_t>(P.n_tiles, 1)));
       P.sync_window = env_int("NXF_K1_SYNC_WINDOW", 1);
+      if (P.num_qt == 1) {
+        // one query tile: nothing is shared between clusters, so every cluster streams one contiguous chunk, unsynchronised
+        P.round_tiles = static_cast<int>(std::max<int64_t>(P.n_tiles, 1));
+        P.sync_window = 0;
+      }
     }
     P.chunks = static_cast<int>(ceil_div64(std::max<int64_t>(P.n_tiles, 1), P.round_tiles));  // reported as "chunks": rounds per launch
     P.cap = 2 * P.k_fetch + 256;  // pruned between tiles once fewer than 256 (one tile of appends) slots are left
