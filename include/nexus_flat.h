@@ -91,13 +91,15 @@ enum {
   NXF_SEARCH_FORCE_STREAM = 1 << 1,  /* small-batch HBM-streaming kernel (K2); nq <= NXF_STREAM_MAX_NQ */
   NXF_SEARCH_FORCE_TENSOR = 1 << 2,  /* tcgen05 GEMM + fused top-k (K1); needs f16/bf16 storage */
   NXF_SEARCH_NO_RESCORE = 1 << 3,    /* K1 only: skip the fp32-query re-score of the over-fetched candidates */
-  NXF_SEARCH_TENSOR_1CTA = 1 << 4    /* K1 only: cta_group::1 tiles (debug / A-B comparison) */
+  NXF_SEARCH_TENSOR_1CTA = 1 << 4,   /* K1 only: cta_group::1 tiles (debug / A-B comparison) */
+  NXF_SEARCH_FORCE_TSTREAM = 1 << 5  /* small-batch tcgen05 streaming kernel (K2T); nq <= 128, f16/bf16 storage */
 };
 #define NXF_STREAM_MAX_NQ 4
+#define NXF_TSTREAM_MAX_NQ 128
 #define NXF_MAX_K 2048
 
 /* which kernel family served the last search on this handle (nxf_stats.last_path) */
-enum { NXF_PATH_NONE = 0, NXF_PATH_STREAM = 1, NXF_PATH_TENSOR = 2, NXF_PATH_EXACT = 3 };
+enum { NXF_PATH_NONE = 0, NXF_PATH_STREAM = 1, NXF_PATH_TENSOR = 2, NXF_PATH_EXACT = 3, NXF_PATH_TSTREAM = 4 };
 
 typedef struct nxf_stats {
   int64_t kernel_launches; /* number of this library's kernels launched on behalf of the handle */

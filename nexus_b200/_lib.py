@@ -24,10 +24,11 @@ SEARCH_FORCE_STREAM = 1 << 1
 SEARCH_FORCE_TENSOR = 1 << 2
 SEARCH_NO_RESCORE = 1 << 3
 SEARCH_TENSOR_1CTA = 1 << 4
+SEARCH_FORCE_TSTREAM = 1 << 5
 STREAM_MAX_NQ = 4
 MAX_K = 2048
-PATH_NONE, PATH_STREAM, PATH_TENSOR, PATH_EXACT = 0, 1, 2, 3
-PATH_NAMES = {0: "none", 1: "stream", 2: "tensor", 3: "exact"}
+PATH_NONE, PATH_STREAM, PATH_TENSOR, PATH_EXACT, PATH_TSTREAM = 0, 1, 2, 3, 4
+PATH_NAMES = {0: "none", 1: "stream", 2: "tensor", 3: "exact", 4: "tstream"}
 
 EXPORTS = [
     "nxf_version", "nxf_last_error", "nxf_device_count", "nxf_create", "nxf_destroy", "nxf_reset", "nxf_reserve",

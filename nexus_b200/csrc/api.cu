@@ -431,10 +431,29 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
   if (flags & NXF_SEARCH_FORCE_EXACT) path = NXF_PATH_EXACT;
   else if (flags & NXF_SEARCH_FORCE_STREAM) path = NXF_PATH_STREAM;
   else if (flags & NXF_SEARCH_FORCE_TENSOR) path = NXF_PATH_TENSOR;
+  else if (flags & NXF_SEARCH_FORCE_TSTREAM) path = NXF_PATH_TSTREAM;
+  else if (store16 && nq >= env_int("NXF_TSTREAM_MIN_NQ", 2) && nq <= NXF_TSTREAM_MAX_NQ) path = NXF_PATH_TSTREAM;
   else if (nq <= NXF_STREAM_MAX_NQ) path = NXF_PATH_STREAM;
   else path = store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
 
   const int64_t row_bytes = idx->ld * dtype_size(idx->store_dtype);
+  if (path == NXF_PATH_TSTREAM) {
+    // K2T keeps the (16-padded) queries resident in shared memory; if that leaves fewer than 4 ring stages, or the storage is
+    // fp32, fall back to the kernels that do not need it
+    const int nq_pad = static_cast<int>(round_up64(std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ), 16));
+    const int st = store16 ? k2t_plan_stages(static_cast<int>(idx->ld / 64), nq_pad) : 0;
+    if (st == 0) {
+      if (flags & NXF_SEARCH_FORCE_TSTREAM) {
+        set_error("nxf_search: the tensor stream kernel needs f16/bf16 storage and queries that fit in shared memory (nq=%lld, dim=%d)",
+                  (long long)nq, idx->dim);
+        return NXF_EUNSUPPORTED;
+      }
+      path = nq <= NXF_STREAM_MAX_NQ ? NXF_PATH_STREAM : (store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT);
+    } else {
+      P.stages = st;
+      P.nq_t = nq_pad;
+    }
+  }
   if (path == NXF_PATH_STREAM) {
     // rows per consumer warp per stage: keep a stage <= 48 KB and at least two stages in flight
     int rw = 4;
@@ -465,6 +484,20 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.owners = static_cast<int64_t>(P.grid) * 8 * P.nq_t;
     P.arena_stride = static_cast<int64_t>(P.grid) * 8 * P.k_eff;
     P.batch = P.nq_t;
+  } else if (path == NXF_PATH_TSTREAM) {
+    // same query-side rounding as K1: over-fetch and re-score in fp32 unless the queries already are of the storage type
+    if (!(flags & NXF_SEARCH_NO_RESCORE) && q_dtype != idx->store_dtype) {
+      P.rescore = 1;
+      int64_t kf = static_cast<int64_t>(P.k_eff) + std::max<int64_t>(16, (P.k_eff + 3) / 4);
+      kf = (kf + 7) / 8 * 8;
+      P.k_fetch = static_cast<int>(std::max<int64_t>(P.k_eff, std::min<int64_t>(std::min<int64_t>(kf, NXF_MAX_K), idx->n)));
+    }
+    P.n_tiles = ceil_div64(idx->n, 128);
+    P.grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(idx->sm_count, P.n_tiles)));
+    P.cap = 2 * P.k_fetch + 256;   // pruned between tiles once more than 2k' entries are held
+    P.owners = static_cast<int64_t>(P.grid) * P.nq_t;
+    P.arena_stride = static_cast<int64_t>(P.grid) * P.k_fetch;
+    P.batch = std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ);
   } else if (path == NXF_PATH_EXACT) {
     P.n_tiles = ceil_div64(idx->n, 128);
     P.num_qt = static_cast<int>(ceil_div64(nq, 128));
@@ -539,7 +572,8 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   if (rc) return rc;
   if (q_ld == 0) q_ld = idx->dim;
   NXF_REQUIRE(q_ld >= idx->dim, "nxf_search: query stride %lld smaller than dim %d", (long long)q_ld, idx->dim);
-  const int nforce = !!(flags & NXF_SEARCH_FORCE_EXACT) + !!(flags & NXF_SEARCH_FORCE_STREAM) + !!(flags & NXF_SEARCH_FORCE_TENSOR);
+  const int nforce = !!(flags & NXF_SEARCH_FORCE_EXACT) + !!(flags & NXF_SEARCH_FORCE_STREAM) + !!(flags & NXF_SEARCH_FORCE_TENSOR) +
+                     !!(flags & NXF_SEARCH_FORCE_TSTREAM);
   NXF_REQUIRE(nforce <= 1, "nxf_search: more than one NXF_SEARCH_FORCE_* flag");
 
   std::lock_guard<std::mutex> lk(idx->mu);
@@ -568,6 +602,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     if (rc) return rc;
     if (idx->n == 0) break;
     if (P.path == NXF_PATH_STREAM) { batch = std::min<int64_t>(nq, P.batch); break; }
+    if (P.path == NXF_PATH_TSTREAM) { batch = std::min<int64_t>(nq, P.batch); break; }
     if (P.path == NXF_PATH_TENSOR && P.batch < batch) { batch = P.batch; continue; }  // re-plan for the per-launch query count
     const int64_t budget = (int64_t(6) << 30) << (it >= 6 ? 1 : 0);  // last tries: accept a larger arena
     const int64_t per_q = std::max<int64_t>(P.arena_stride * 8, 1);
@@ -589,7 +624,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     Carver cv(base);
     q_src = q_on_device ? nullptr : cv.take<unsigned char>(static_cast<size_t>(batch) * q_ld * qsz);
     q_f32 = cv.take<float>(static_cast<size_t>(nq_pad) * idx->ld);
-    q16 = (P.path == NXF_PATH_TENSOR) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld) : nullptr;
+    q16 = (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld) : nullptr;
     tau_g = cv.take<uint32_t>(static_cast<size_t>(3 * nq_pad + 64));  // tau | qcnt | lock | K1 round counter
     qcnt = tau_g ? tau_g + nq_pad : nullptr;
     qlock = tau_g ? tau_g + 2 * nq_pad : nullptr;
@@ -618,7 +653,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     rc = launch_convert_rows(q_dev, q_dtype, q_ld, q_f32, NXF_F32, idx->ld, bn, idx->dim, stream);
     if (rc) return rc;
     idx->stats.kernel_launches++;
-    if (P.path == NXF_PATH_TENSOR) {
+    if (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) {
       rc = launch_convert_rows(q_dev, q_dtype, q_ld, q16, idx->store_dtype, idx->ld, bn, idx->dim, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
@@ -649,6 +684,19 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
         if (rc) return rc;
         idx->stats.kernel_launches++;
       }
+    } else if (P.path == NXF_PATH_TSTREAM) {
+      K2TParams kp;
+      kp.n = idx->n; kp.nq = static_cast<int>(bn); kp.nq_pad = static_cast<int>(round_up64(bn, 16)); kp.kblocks = static_cast<int>(idx->ld / 64);
+      kp.stages = k2t_plan_stages(kp.kblocks, kp.nq_pad);
+      kp.tbuf_stride = kp.nq_pad <= 32 ? 32 : (kp.nq_pad <= 64 ? 64 : 128);
+      kp.tbufs = std::min(8, 512 / kp.tbuf_stride);
+      kp.half_norm = l2 ? idx->half_norm : nullptr;
+      kp.sink = sink;
+      kp.sink.cap = P.cap;
+      // the candidate buffers are laid out [cta][nq_pad of THIS launch][cap]; the plan sized them for the largest launch
+      rc = launch_k2t(idx->store_dtype, q16, bn, idx->data, idx->ld, kp, P.grid, stream);
+      if (rc) return rc;
+      idx->stats.kernel_launches++;
     } else if (P.path == NXF_PATH_EXACT) {
       KxParams kp;
       kp.q = q_f32; kp.ldq = idx->ld; kp.corpus = idx->data; kp.ld = idx->ld; kp.half_norm = l2 ? idx->half_norm : nullptr;

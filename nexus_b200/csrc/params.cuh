@@ -51,6 +51,18 @@ struct K2Params {
   SinkParams sink;
 };
 
+struct K2TParams {
+  int64_t n;     // corpus rows
+  int nq;        // queries (<= 128)
+  int nq_pad;    // nq rounded up to 16 = UMMA N
+  int kblocks;   // ld / 64
+  int stages;    // ring depth
+  int tbufs;     // TMEM accumulator buffers
+  int tbuf_stride;  // TMEM columns between buffers
+  const float* half_norm;
+  SinkParams sink;
+};
+
 struct MergeArenaParams {
   const Entry* arena;
   const uint32_t* qcnt;
@@ -87,6 +99,10 @@ int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, 
 int k1_smem_bytes(int cta_group);
 int launch_k2(int store_dtype, const K2Params& p, int nq_t, int rw, int grid, size_t smem, cudaStream_t stream);
 size_t k2_smem_bytes(int64_t ld, int elem_size, int nq_t, int rw, int stages);
+int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* corpus, int64_t ld, const K2TParams& p, int grid,
+               cudaStream_t stream);
+size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages);
+int k2t_plan_stages(int kblocks, int nq_pad);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,

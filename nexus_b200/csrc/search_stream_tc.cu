@@ -1,0 +1,302 @@
+// search_stream_tc.cu -- K2T: small-batch (nq <= 128) exact search on tcgen05 with the CORPUS as the M operand.
+//
+// The shape in which the reference calls search today is a handful of queries against the whole corpus: 32-row
+// chunks (Nexus/evaluation/text_retrieval/utils.py:221-224), 128 users per recsys batch
+// (Nexus/inference/embedder/recommendation/base.py:182), one query per request
+// (serve/inference_service_text_retrieval.py:70).  Every such call is one pass over the corpus, i.e. bound by HBM
+// bandwidth: algorithmic bytes = N*ld*2 per launch.  CUDA-core FMAs stop keeping up with HBM beyond one or two
+// queries, so the dot products go to the tensor cores -- but, unlike K1, with the roles swapped:
+//   A (M = 128)  = 128 corpus rows, streamed by TMA through a shared-memory ring, 16 KB per 64-wide K block
+//   B (N = nq')  = the queries (nq rounded up to 16), loaded ONCE and resident in shared memory for the whole launch
+//   D in TMEM    = [128 corpus rows x nq'] fp32, several buffers deep
+// so shared memory and L2 only ever carry the corpus, once.  The epilogue thread owns a corpus row and compares its
+// nq' scores with the per-query thresholds kept in shared memory (v - tau > 0 on a max tree); survivors are appended
+// to per-(CTA, query) candidate buffers with a shared-memory atomic counter.  A named barrier with an OR reduction
+// once per tile decides (uniformly) whether any buffer must be pruned before the next tile.
+#include "params.cuh"
+
+namespace nxf {
+
+namespace k2t {
+constexpr int BLOCK_M = 128;   // corpus rows per tile
+constexpr int BLOCK_K = 64;
+constexpr int UMMA_K = 16;
+constexpr int THREADS = 256;
+constexpr int EPI_WARP0 = 4;
+constexpr int EPI_THREADS = 128;
+constexpr int TMEM_COLS = 512;
+constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB per stage
+constexpr int MAX_STAGES = 12;
+constexpr int MAX_TBUF = 8;
+constexpr int MAX_NQ = 128;
+// shared memory after the 1024-aligned (queries | ring): barriers, tau, counts, prune histograms
+constexpr int TAIL_BYTES = (2 * MAX_STAGES + 2 * MAX_TBUF + 2) * 8 + 16 + MAX_NQ * 4 * 2 + 4 * 256 * 4;
+}  // namespace k2t
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait_dep16(uint32_t (&r)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                 "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+               :
+               : "memory");
+}
+// named barrier 1 over the 128 epilogue threads with an OR reduction of a predicate
+__device__ __forceinline__ bool epi_bar_or(bool pred) {
+  uint32_t r;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\t"
+      "barrier.cta.red.or.pred.aligned q, 1, 128, p;\n\t"
+      "selp.u32 %0, 1, 0, q;\n\t}"
+      : "=r"(r) : "r"(static_cast<uint32_t>(pred)) : "memory");
+  return r != 0;
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("barrier.cta.sync.aligned 1, 128;" ::: "memory"); }
+
+template <bool BF16>
+__global__ void __launch_bounds__(k2t::THREADS, 1)
+k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K2TParams p) {
+  using namespace k2t;
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int q_bytes = p.kblocks * p.nq_pad * 128;          // resident queries: [kblocks][nq_pad rows][128 B], 1024-aligned blocks
+  unsigned char* q_smem = smem;
+  unsigned char* ring = smem + ((q_bytes + 1023) & ~1023);
+  unsigned char* tail = ring + p.stages * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty = full + MAX_STAGES;
+  uint64_t* tfull = empty + MAX_STAGES;
+  uint64_t* tempty = tfull + MAX_TBUF;
+  uint64_t* qfull = tempty + MAX_TBUF;
+  uint32_t* tmem_ptr_s = reinterpret_cast<uint32_t*>(qfull + 2);
+  float* tau_s = reinterpret_cast<float*>(tmem_ptr_s + 4);  // [MAX_NQ]
+  int* cnt_s = reinterpret_cast<int*>(tau_s + MAX_NQ);      // [MAX_NQ]
+  uint32_t* hist = reinterpret_cast<uint32_t*>(cnt_s + MAX_NQ);
+
+  const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
+  const unsigned lane = lane_id();
+  const int64_t n_tiles = (p.n + BLOCK_M - 1) / BLOCK_M;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_q);
+    tma_prefetch_desc(&tmap_c);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int b = 0; b < p.tbufs; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
+    mbar_init(qfull, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<1>(tmem_ptr_s, TMEM_COLS);
+  if (threadIdx.x < MAX_NQ) {
+    tau_s[threadIdx.x] = (static_cast<int>(threadIdx.x) < p.nq) ? tau_load(p.sink.tau_g, threadIdx.x) : INFINITY;  // padded columns accept nothing
+    cnt_s[threadIdx.x] = 0;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_ptr_s);
+
+  if (warp == 0) {
+    // ============================== TMA producer ==============================
+    if (lane == 0) {
+      mbar_expect_tx(qfull, static_cast<uint32_t>(q_bytes));
+      for (int kb = 0; kb < p.kblocks; ++kb) tma_load_2d(&tmap_q, qfull, q_smem + kb * p.nq_pad * 128, kb * BLOCK_K, 0, kEvictLast);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int32_t row0 = static_cast<int32_t>(t * BLOCK_M);
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_expect_tx(&full[s], A_BYTES);
+          tma_load_2d(&tmap_c, &full[s], ring + s * A_BYTES, kb * BLOCK_K, row0, kEvictFirst);
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ============================== MMA issuer ==============================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M, p.nq_pad);
+      mbar_wait(qfull, 0);
+      tc_fence_after();
+      int s = 0;
+      uint32_t ph = 0;
+      uint32_t iter = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++iter) {
+        const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
+        mbar_wait(&tempty[b], bph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + b * p.tbuf_stride;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint64_t a_desc = umma_desc_sw128(smem_u32(ring + s * A_BYTES));
+          const uint64_t b_desc = umma_desc_sw128(smem_u32(q_smem + kb * p.nq_pad * 128));
+#pragma unroll
+          for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4)
+            umma_f16<1>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, (kb | k4) != 0 ? 1u : 0u);
+          umma_commit<1>(&empty[s]);
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+        umma_commit<1>(&tfull[b]);
+      }
+    }
+    __syncwarp();
+  } else if (warp >= EPI_WARP0) {
+    // ============================== epilogue ==============================
+    const int ew = warp - EPI_WARP0;
+    const int et = ew * 32 + static_cast<int>(lane);  // 0..127: epilogue thread == corpus row within the tile == query it looks after
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
+    uint32_t* my_hist = hist + ew * 256;
+    const int cap = p.sink.cap;
+    const int k = p.sink.k;
+    Entry* cta_cand = p.sink.cand + static_cast<int64_t>(blockIdx.x) * p.nq_pad * cap;  // [nq_pad][cap]
+    uint32_t* cand_words = reinterpret_cast<uint32_t*>(cta_cand);
+    const int chunks = p.nq_pad / 16;
+    uint32_t iter = 0;
+    float tau_next = (et < p.nq) ? tau_load(p.sink.tau_g, et) : INFINITY;
+
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++iter) {
+      const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
+      const int64_t row = t * BLOCK_M + et;
+      const bool row_ok = row < p.n;
+      const float hn = (p.half_norm != nullptr && row_ok) ? p.half_norm[row] : 0.f;
+      mbar_wait(&tfull[b], bph);
+      tc_fence_after();
+      const uint32_t tbase = taddr + b * p.tbuf_stride;
+#pragma unroll 1
+      for (int ch = 0; ch < chunks; ++ch) {
+        uint32_t vr[16];
+        tmem_ld16(tbase + ch * 16, vr);
+        tmem_ld_wait_dep16(vr);
+        if (ch == chunks - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[b]);
+        }
+        float v[16], d[16];
+        const float4* tp = reinterpret_cast<const float4*>(tau_s + ch * 16);
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4) {
+          const float4 tq = tp[j4];  // same address for every lane: broadcast
+          v[4 * j4] = __uint_as_float(vr[4 * j4]) - hn;
+          v[4 * j4 + 1] = __uint_as_float(vr[4 * j4 + 1]) - hn;
+          v[4 * j4 + 2] = __uint_as_float(vr[4 * j4 + 2]) - hn;
+          v[4 * j4 + 3] = __uint_as_float(vr[4 * j4 + 3]) - hn;
+          d[4 * j4] = v[4 * j4] - tq.x;
+          d[4 * j4 + 1] = v[4 * j4 + 1] - tq.y;
+          d[4 * j4 + 2] = v[4 * j4 + 2] - tq.z;
+          d[4 * j4 + 3] = v[4 * j4 + 3] - tq.w;
+        }
+        float m = fmax3(d[0], d[1], d[2]);
+#pragma unroll
+        for (int j = 3; j < 15; j += 2) m = fmax3(m, d[j], d[j + 1]);
+        m = fmaxf(m, d[15]);
+        if (m > 0.f && row_ok) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (d[j] > 0.f) {  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
+              const int qi = ch * 16 + j;
+              const int pos = atomicAdd(&cnt_s[qi], 1);
+              const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
+              cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
+              cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
+            }
+          }
+        }
+      }
+      // ---- once per tile: does any query's buffer risk overflowing during the next tile (<= 128 appends)? ----
+      // The count read here may miss appends of warps that are still inside the tile (<= 128 per query and tile in total),
+      // hence the margin of two tiles; the barrier orders all appends before the exact re-read below.
+      const bool any_full = epi_bar_or(et < p.nq && cnt_s[et] > cap - 2 * BLOCK_M);
+      if (any_full) {
+        // all appends of this tile are visible now; warp w prunes queries w, w+4, ...
+        for (int qi = ew; qi < p.nq; qi += 4) {
+          const int n_q = cnt_s[qi];
+          if (n_q > cap - 2 * BLOCK_M && n_q > k) {
+            const uint32_t kth = warp_prune(cta_cand + static_cast<int64_t>(qi) * cap, n_q, k, my_hist);
+            if (lane == 0) {
+              cnt_s[qi] = k;
+              tau_s[qi] = fmaxf(tau_s[qi], okey_inv(kth));
+              atomicMax(&p.sink.tau_g[qi], kth);
+            }
+            __syncwarp();
+          }
+        }
+        epi_bar_sync();
+      }
+      // other CTAs' progress: thread et looks after query et (value loaded one tile ago)
+      if (et < p.nq) {
+        if (tau_next > tau_s[et]) tau_s[et] = tau_next;
+        tau_next = tau_load(p.sink.tau_g, et);
+      }
+    }
+
+    // ---- end: prune every query to k and flush to the arena ----
+    epi_bar_sync();
+    for (int qi = ew; qi < p.nq; qi += 4) {
+      int n_q = cnt_s[qi];
+      Entry* buf = cta_cand + static_cast<int64_t>(qi) * cap;
+      if (n_q > k) {
+        const uint32_t kth = warp_prune(buf, n_q, k, my_hist);
+        if (lane == 0) atomicMax(&p.sink.tau_g[qi], kth);
+        n_q = k;
+      }
+      __syncwarp();
+      warp_flush(p.sink, buf, n_q, qi);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<1>(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+int make_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, int64_t ld, int box_rows, bool bf16);  // search_tc.cu
+
+size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages) {
+  const size_t q_bytes = (static_cast<size_t>(kblocks) * nq_pad * 128 + 1023) & ~size_t(1023);
+  return 1024 + q_bytes + static_cast<size_t>(stages) * k2t::A_BYTES + k2t::TAIL_BYTES;
+}
+
+// Picks the ring depth; returns 0 when the resident queries leave room for fewer than 4 stages (caller uses K1 instead).
+int k2t_plan_stages(int kblocks, int nq_pad) {
+  for (int st = k2t::MAX_STAGES; st >= 4; --st)
+    if (k2t_smem_bytes(kblocks, nq_pad, st) <= 227 * 1024) return st;
+  return 0;
+}
+
+int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* corpus, int64_t ld, const K2TParams& p, int grid,
+               cudaStream_t stream) {
+  const bool bf16 = store_dtype == NXF_BF16;
+  if (store_dtype != NXF_BF16 && store_dtype != NXF_F16) { set_error("tensor stream search needs f16/bf16 storage"); return NXF_EUNSUPPORTED; }
+  CUtensorMap tq, tc;
+  int rc = make_tmap_2d_sw128(&tq, q16, nq_rows, ld, p.nq_pad, bf16);
+  if (rc) return rc;
+  rc = make_tmap_2d_sw128(&tc, corpus, p.n, ld, k2t::BLOCK_M, bf16);
+  if (rc) return rc;
+  const size_t smem = k2t_smem_bytes(p.kblocks, p.nq_pad, p.stages);
+  if (bf16) {
+    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    k2t_stream_kernel<true><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);
+  } else {
+    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    k2t_stream_kernel<false><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);
+  }
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
+}  // namespace nxf

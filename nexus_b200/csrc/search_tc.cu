@@ -444,7 +444,7 @@ static PFN_encodeTiled get_encode_fn() {
 }
 
 // rows x ld 16-bit matrix, box = 64 elements (128 B, one swizzle atom) x box_rows
-static int make_tmap(CUtensorMap* m, const void* base, int64_t rows, int64_t ld, int box_rows, bool bf16) {
+int make_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, int64_t ld, int box_rows, bool bf16) {
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return NXF_ECUDA; }
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(ld), static_cast<cuuint64_t>(rows)};
@@ -485,9 +485,9 @@ int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, 
   const bool bf16 = store_dtype == NXF_BF16;
   if (store_dtype != NXF_BF16 && store_dtype != NXF_F16) { set_error("tensor-core search needs f16/bf16 storage"); return NXF_EUNSUPPORTED; }
   CUtensorMap tq, tc;
-  int rc = make_tmap(&tq, q16, nq_rows, ld, k1::BLOCK_M, bf16);
+  int rc = make_tmap_2d_sw128(&tq, q16, nq_rows, ld, k1::BLOCK_M, bf16);
   if (rc) return rc;
-  rc = make_tmap(&tc, corpus, p.n, ld, k1::BLOCK_N / cta_group, bf16);
+  rc = make_tmap_2d_sw128(&tc, corpus, p.n, ld, k1::BLOCK_N / cta_group, bf16);
   if (rc) return rc;
   if (cta_group == 2) return bf16 ? launch_k1_t<2, true>(tq, tc, p, grid, stream) : launch_k1_t<2, false>(tq, tc, p, grid, stream);
   return bf16 ? launch_k1_t<1, true>(tq, tc, p, grid, stream) : launch_k1_t<1, false>(tq, tc, p, grid, stream);

@@ -13,6 +13,8 @@ FLAGS = {
     "tensor": L.SEARCH_FORCE_TENSOR,
     "tensor_raw": L.SEARCH_FORCE_TENSOR | L.SEARCH_NO_RESCORE,
     "tensor_1cta": L.SEARCH_FORCE_TENSOR | L.SEARCH_TENSOR_1CTA,
+    "tstream": L.SEARCH_FORCE_TSTREAM,
+    "tstream_raw": L.SEARCH_FORCE_TSTREAM | L.SEARCH_NO_RESCORE,
 }
 
 
@@ -41,7 +43,7 @@ def run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, atol=1e-6, min_r
         assert st["last_path_name"] == expect_path, st
     cs = stored(c, store)
     xs = x.astype(np.float32)
-    if path == "tensor_raw":
+    if path in ("tensor_raw", "tstream_raw"):
         xs = stored(xs, store)          # the MMA sees the queries rounded to the storage type
     if metric == "ip":
         ref_s, ref_i = oracle.blocked_ip_search(cs, xs, k, pad=True)

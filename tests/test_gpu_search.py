@@ -82,7 +82,30 @@ def test_exact_kernel(case, store):
 def test_stream_kernel(case, nq, store):
     n, d, k = case
     c, x = gen_inputs(n, d, nq, seed=200 + d)
-    run_and_check(c, x, k, store=store, path="auto", expect_path="stream")
+    # 16-bit storage with more than one query goes to the tensor-core streaming kernel (K2T); K2 keeps nq = 1 and fp32 storage
+    run_and_check(c, x, k, store=store, path="auto", expect_path="stream" if (store == "f32" or nq == 1) else "tstream")
+    if store != "f32" and nq > 1:
+        run_and_check(c, x, k, store=store, path="stream", expect_path="stream")
+
+
+@pytest.mark.parametrize("store", ["bf16", "f16"])
+@pytest.mark.parametrize("case", [
+    # N, D, Q, k
+    (3000, 64, 2, 10), (3000, 64, 16, 10), (5000, 128, 17, 100), (20000, 384, 33, 10), (9000, 768, 64, 100),
+    (4096, 96, 100, 500), (2500, 100, 5, 7), (130, 64, 128, 200), (40000, 64, 128, 500), (7001, 1536, 32, 10),
+])
+def test_tensor_stream_kernel(case, store):
+    """K2T (corpus as the M operand, queries resident in shared memory): default dispatch for 2 <= nq <= 128 on 16-bit storage."""
+    n, d, q, k = case
+    c, x = gen_inputs(n, d, q, seed=500 + n % 79)
+    run_and_check(c, x, k, store=store, path="auto", rtol=1e-5, expect_path="tstream", min_recall=0.999)
+    run_and_check(c, x, k, store=store, path="tstream_raw", rtol=2e-4, atol=2e-5, expect_path="tstream", min_recall=0.999)
+
+
+def test_tensor_stream_falls_back_when_queries_do_not_fit():
+    """128 queries x 1536 dims = 393 KB of resident queries: K2T is not eligible, the search is served by K1."""
+    c, x = gen_inputs(6000, 1536, 128, seed=9)
+    run_and_check(c, x, 10, store="bf16", path="auto", expect_path="tensor", min_recall=0.999)
 
 
 @pytest.mark.parametrize("store", ["bf16", "f16"])
