@@ -432,7 +432,11 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
   else if (flags & NXF_SEARCH_FORCE_STREAM) path = NXF_PATH_STREAM;
   else if (flags & NXF_SEARCH_FORCE_TENSOR) path = NXF_PATH_TENSOR;
   else if (flags & NXF_SEARCH_FORCE_TSTREAM) path = NXF_PATH_TSTREAM;
-  else if (store16 && nq >= env_int("NXF_TSTREAM_MIN_NQ", 2) && nq <= NXF_TSTREAM_MAX_NQ) path = NXF_PATH_TSTREAM;
+  // K2 (CUDA cores, whole-row bulk copies) keeps single queries on long rows, where it already runs at the HBM roofline; short
+  // rows leave most of its lanes idle, so they go to K2T even for one query
+  else if (store16 && nq <= NXF_TSTREAM_MAX_NQ &&
+           nq >= env_int("NXF_TSTREAM_MIN_NQ", idx->ld * dtype_size(idx->store_dtype) < 512 ? 1 : 2))
+    path = NXF_PATH_TSTREAM;
   else if (nq <= NXF_STREAM_MAX_NQ) path = NXF_PATH_STREAM;
   else path = store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
 
@@ -494,7 +498,9 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     }
     P.n_tiles = ceil_div64(idx->n, 128);
     P.grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(idx->sm_count, P.n_tiles)));
-    P.cap = 2 * P.k_fetch + 256;   // pruned between tiles once more than 2k' entries are held
+    // overflow checks every `ce` tiles: short rows (few K blocks per tile) cannot afford a barrier per tile
+    P.rw = std::max(1, std::min(8, 16 / std::max<int>(1, static_cast<int>(idx->ld / 64))));
+    P.cap = 2 * P.k_fetch + 2 * 128 * P.rw;   // pruned once more than 2k' entries are held
     P.owners = static_cast<int64_t>(P.grid) * P.nq_t;
     P.arena_stride = static_cast<int64_t>(P.grid) * P.k_fetch;
     P.batch = std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ);
@@ -691,6 +697,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.tbuf_stride = kp.nq_pad <= 32 ? 32 : (kp.nq_pad <= 64 ? 64 : 128);
       kp.tbufs = std::min(8, 512 / kp.tbuf_stride);
       kp.half_norm = l2 ? idx->half_norm : nullptr;
+      kp.check_every = P.rw;
       kp.sink = sink;
       kp.sink.cap = P.cap;
       // the candidate buffers are laid out [cta][nq_pad of THIS launch][cap]; the plan sized them for the largest launch
@@ -713,8 +720,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
       kp.sink = sink;
-      kp.n_tiles = P.n_tiles; kp.round_tiles = P.round_tiles; kp.sync_window = P.sync_window;
-      kp.sync_ctr = tau_g + 3 * nq_pad;
+      kp.round_tiles = P.round_tiles; kp.sync_window = P.sync_window;
       // the last launch of a multi-batch search may hold fewer query tiles than planned: never more clusters than tile-units
       int grid = P.grid;
       {
@@ -723,9 +729,29 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       }
       NXF_REQUIRE(kp.num_qt <= grid / P.cta_group || P.n_tiles == 0, "nxf_search: internal: %d query tiles for %d clusters", kp.num_qt,
                   grid / P.cta_group);
-      rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
-      if (rc) return rc;
-      idx->stats.kernel_launches++;
+      // Seeded passes (DESIGN.md "threshold seeding"): a short prefix of the corpus first; its end-of-pass merge leaves every
+      // query's exact k'-th best of that prefix in tau_g, so the next, 32x longer pass starts with a threshold that already
+      // rejects all but ~32 k' scores per query, and the rest of the corpus one that rejects all but ~(N/prefix) k'.
+      int64_t bounds[4] = {0, 0, 0, P.n_tiles};
+      int n_pass = 0;
+      {
+        const int64_t a = std::min<int64_t>(P.n_tiles, P.round_tiles), b = std::min<int64_t>(P.n_tiles, 32 * a);
+        int64_t cuts[2] = {a, b};
+        int64_t prev = 0;
+        // measured on C2: the seed passes pay for themselves only when k' is large (NXF_K1_SEED=0/1 overrides)
+        const int seed_env = env_int("NXF_K1_SEED", -1);
+        const bool seed = seed_env >= 0 ? seed_env != 0 : P.k_fetch >= 512;
+        for (int c = 0; c < 2; ++c)
+          if (seed && kp.num_qt > 1 && cuts[c] > prev && 4 * cuts[c] <= P.n_tiles) { bounds[++n_pass] = cuts[c]; prev = cuts[c]; }
+        bounds[++n_pass] = P.n_tiles;
+      }
+      for (int ps = 0; ps < n_pass; ++ps) {
+        kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
+        kp.sync_ctr = tau_g + 3 * nq_pad + ps;   // one round counter per pass (all zeroed above)
+        rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
+        if (rc) return rc;
+        idx->stats.kernel_launches++;
+      }
     }
 
     if (pe0) {

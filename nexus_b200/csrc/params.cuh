@@ -27,7 +27,7 @@ struct K1Params {
   int64_t nq;   // query rows
   int kblocks;  // ld / 64
   int num_qt;   // query tiles of 128*CG rows (<= number of clusters)
-  int64_t n_tiles;     // ceil(n / 256)
+  int64_t tile_begin, tile_end;  // corpus tiles [begin, end) of this pass (a search is 1-3 passes: seed, seed, rest)
   int round_tiles;     // corpus tiles per round (the L2-resident window)
   int sync_window;     // soft round barrier: a producer may run this many rounds ahead of the rest (0 = no barrier)
   uint32_t* sync_ctr;  // [1] zeroed per launch: rounds completed, summed over clusters
@@ -59,6 +59,7 @@ struct K2TParams {
   int stages;    // ring depth
   int tbufs;     // TMEM accumulator buffers
   int tbuf_stride;  // TMEM columns between buffers
+  int check_every;  // tiles between two buffer-overflow checks (cap = 2k' + 2*128*check_every)
   const float* half_norm;
   SinkParams sink;
 };

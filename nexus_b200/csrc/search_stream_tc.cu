@@ -60,7 +60,42 @@ __device__ __forceinline__ bool epi_bar_or(bool pred) {
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("barrier.cta.sync.aligned 1, 128;" ::: "memory"); }
 
-template <bool BF16>
+// One 16-query slice of a corpus row's scores: d = v - tau on a max tree; the common case is one compare, branch not taken.
+template <bool L2>
+__device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], int ch, float hn, int64_t row, bool row_ok,
+                                          const float* __restrict__ tau_s, int* __restrict__ cnt_s,
+                                          uint32_t* __restrict__ cand_words, int cap) {
+  float v[16], d[16];
+  const float4* tp = reinterpret_cast<const float4*>(tau_s + ch * 16);
+#pragma unroll
+  for (int j4 = 0; j4 < 4; ++j4) {
+    const float4 tq = tp[j4];  // same address for every lane: broadcast
+#pragma unroll
+    for (int e = 0; e < 4; ++e) v[4 * j4 + e] = L2 ? __uint_as_float(vr[4 * j4 + e]) - hn : __uint_as_float(vr[4 * j4 + e]);
+    d[4 * j4] = v[4 * j4] - tq.x;
+    d[4 * j4 + 1] = v[4 * j4 + 1] - tq.y;
+    d[4 * j4 + 2] = v[4 * j4 + 2] - tq.z;
+    d[4 * j4 + 3] = v[4 * j4 + 3] - tq.w;
+  }
+  float m = fmax3(d[0], d[1], d[2]);
+#pragma unroll
+  for (int j = 3; j < 15; j += 2) m = fmax3(m, d[j], d[j + 1]);
+  m = fmaxf(m, d[15]);
+  if (m > 0.f && row_ok) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      if (d[j] > 0.f) {  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
+        const int qi = ch * 16 + j;
+        const int pos = atomicAdd(&cnt_s[qi], 1);
+        const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
+        cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
+        cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
+      }
+    }
+  }
+}
+
+template <bool BF16, bool L2>
 __global__ void __launch_bounds__(k2t::THREADS, 1)
 k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K2TParams p) {
   using namespace k2t;
@@ -162,67 +197,56 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     Entry* cta_cand = p.sink.cand + static_cast<int64_t>(blockIdx.x) * p.nq_pad * cap;  // [nq_pad][cap]
     uint32_t* cand_words = reinterpret_cast<uint32_t*>(cta_cand);
     const int chunks = p.nq_pad / 16;
+    const int check_every = p.check_every;           // tiles between two overflow checks / threshold refreshes
+    const int full_mark = cap - 2 * check_every * BLOCK_M;  // == 2k': see the margin note below
     uint32_t iter = 0;
+    int since_check = 0;
     float tau_next = (et < p.nq) ? tau_load(p.sink.tau_g, et) : INFINITY;
 
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++iter) {
       const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
       const int64_t row = t * BLOCK_M + et;
       const bool row_ok = row < p.n;
-      const float hn = (p.half_norm != nullptr && row_ok) ? p.half_norm[row] : 0.f;
+      const float hn = (L2 && row_ok) ? p.half_norm[row] : 0.f;
       mbar_wait(&tfull[b], bph);
       tc_fence_after();
       const uint32_t tbase = taddr + b * p.tbuf_stride;
+      // two register buffers: the tcgen05.ld of slice ch+1 is in flight while slice ch is filtered
+      uint32_t va[16], vb[16];
+      tmem_ld16(tbase, va);
 #pragma unroll 1
-      for (int ch = 0; ch < chunks; ++ch) {
-        uint32_t vr[16];
-        tmem_ld16(tbase + ch * 16, vr);
-        tmem_ld_wait_dep16(vr);
-        if (ch == chunks - 1) {
+      for (int ch = 0; ch < chunks; ch += 2) {
+        tmem_ld_wait_dep16(va);
+        const bool more = ch + 1 < chunks;
+        if (more) tmem_ld16(tbase + (ch + 1) * 16, vb);
+        else {  // accumulator fully read: hand the buffer back to the MMA issuer
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[b]);
         }
-        float v[16], d[16];
-        const float4* tp = reinterpret_cast<const float4*>(tau_s + ch * 16);
-#pragma unroll
-        for (int j4 = 0; j4 < 4; ++j4) {
-          const float4 tq = tp[j4];  // same address for every lane: broadcast
-          v[4 * j4] = __uint_as_float(vr[4 * j4]) - hn;
-          v[4 * j4 + 1] = __uint_as_float(vr[4 * j4 + 1]) - hn;
-          v[4 * j4 + 2] = __uint_as_float(vr[4 * j4 + 2]) - hn;
-          v[4 * j4 + 3] = __uint_as_float(vr[4 * j4 + 3]) - hn;
-          d[4 * j4] = v[4 * j4] - tq.x;
-          d[4 * j4 + 1] = v[4 * j4 + 1] - tq.y;
-          d[4 * j4 + 2] = v[4 * j4 + 2] - tq.z;
-          d[4 * j4 + 3] = v[4 * j4 + 3] - tq.w;
-        }
-        float m = fmax3(d[0], d[1], d[2]);
-#pragma unroll
-        for (int j = 3; j < 15; j += 2) m = fmax3(m, d[j], d[j + 1]);
-        m = fmaxf(m, d[15]);
-        if (m > 0.f && row_ok) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            if (d[j] > 0.f) {  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
-              const int qi = ch * 16 + j;
-              const int pos = atomicAdd(&cnt_s[qi], 1);
-              const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
-              cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
-              cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
-            }
+        k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+        if (more) {
+          tmem_ld_wait_dep16(vb);
+          if (ch + 2 < chunks) tmem_ld16(tbase + (ch + 2) * 16, va);
+          else {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[b]);
           }
+          k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
         }
       }
-      // ---- once per tile: does any query's buffer risk overflowing during the next tile (<= 128 appends)? ----
-      // The count read here may miss appends of warps that are still inside the tile (<= 128 per query and tile in total),
-      // hence the margin of two tiles; the barrier orders all appends before the exact re-read below.
-      const bool any_full = epi_bar_or(et < p.nq && cnt_s[et] > cap - 2 * BLOCK_M);
+      if (++since_check < check_every) continue;
+      since_check = 0;
+      // ---- every check_every tiles: could any query's buffer overflow before the next check? ----
+      // A query gains <= 128 entries per tile, so <= 128*check_every between checks.  The count read here may miss appends of
+      // warps still inside this interval's last tile, hence a margin of TWO intervals; the barrier orders all appends
+      // before the exact re-read below.
+      const bool any_full = epi_bar_or(et < p.nq && cnt_s[et] > full_mark);
       if (any_full) {
-        // all appends of this tile are visible now; warp w prunes queries w, w+4, ...
-        for (int qi = ew; qi < p.nq; qi += 4) {
+        for (int qi = ew; qi < p.nq; qi += 4) {  // warp w prunes queries w, w+4, ...
           const int n_q = cnt_s[qi];
-          if (n_q > cap - 2 * BLOCK_M && n_q > k) {
+          if (n_q > full_mark && n_q > k) {
             const uint32_t kth = warp_prune(cta_cand + static_cast<int64_t>(qi) * cap, n_q, k, my_hist);
             if (lane == 0) {
               cnt_s[qi] = k;
@@ -234,7 +258,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         }
         epi_bar_sync();
       }
-      // other CTAs' progress: thread et looks after query et (value loaded one tile ago)
+      // other CTAs' progress: thread et looks after query et (value loaded one interval ago)
       if (et < p.nq) {
         if (tau_next > tau_s[et]) tau_s[et] = tau_next;
         tau_next = tau_load(p.sink.tau_g, et);
@@ -288,13 +312,17 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* co
   rc = make_tmap_2d_sw128(&tc, corpus, p.n, ld, k2t::BLOCK_M, bf16);
   if (rc) return rc;
   const size_t smem = k2t_smem_bytes(p.kblocks, p.nq_pad, p.stages);
-  if (bf16) {
-    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    k2t_stream_kernel<true><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);
-  } else {
-    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    k2t_stream_kernel<false><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);
-  }
+  const bool l2 = p.half_norm != nullptr;
+#define NXF_K2T_LAUNCH(B, L)                                                                                                          \
+  do {                                                                                                                                \
+    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));     \
+    k2t_stream_kernel<B, L><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);                                                         \
+  } while (0)
+  if (bf16 && l2) NXF_K2T_LAUNCH(true, true);
+  else if (bf16) NXF_K2T_LAUNCH(true, false);
+  else if (l2) NXF_K2T_LAUNCH(false, true);
+  else NXF_K2T_LAUNCH(false, false);
+#undef NXF_K2T_LAUNCH
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
 }

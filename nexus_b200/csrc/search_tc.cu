@@ -134,7 +134,7 @@ struct RoundPiece {
 };
 __device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0, int64_t cluster_id, int64_t num_clusters) {
   RoundPiece rp;
-  rp.R = min(static_cast<int64_t>(p.round_tiles), p.n_tiles - r0);
+  rp.R = min(static_cast<int64_t>(p.round_tiles), p.tile_end - r0);
   rp.a = cluster_id * p.num_qt * rp.R / num_clusters;
   rp.b = (cluster_id + 1) * p.num_qt * rp.R / num_clusters;
   return rp;
@@ -185,7 +185,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       int s = 0;
       uint32_t ph = 0;
       int64_t ri = 0;
-      for (int64_t r0 = 0; r0 < p.n_tiles; r0 += p.round_tiles, ++ri) {
+      for (int64_t r0 = p.tile_begin; r0 < p.tile_end; r0 += p.round_tiles, ++ri) {
         if (p.sync_window > 0 && rank == 0 && ri >= p.sync_window) {
           // soft round barrier: wait until (on average) every cluster finished issuing round ri - window; bounded spin, so a
           // cluster that is not resident (foreign kernels on some SMs) costs lockstep, never progress
@@ -229,7 +229,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       int s = 0;
       uint32_t ph = 0;
       uint32_t iter = 0;
-      for (int64_t r0 = 0; r0 < p.n_tiles; r0 += p.round_tiles) {
+      for (int64_t r0 = p.tile_begin; r0 < p.tile_end; r0 += p.round_tiles) {
         const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
         for (int64_t i = rp.a; i < rp.b; ++i, ++iter) {  // one accumulator tile per line position, whatever its query tile
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
@@ -288,7 +288,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     int cur_slot = 0;
     uint32_t iter = 0;
 
-    for (int64_t r0 = 0; r0 < p.n_tiles; r0 += p.round_tiles) {
+    for (int64_t r0 = p.tile_begin; r0 < p.tile_end; r0 += p.round_tiles) {
       const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
       for (int64_t pos = rp.a; pos < rp.b;) {
         const int64_t qt = pos / rp.R;
@@ -371,7 +371,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
     }
 
-    // ---- end of the launch: fold both slots' rows into the per-query global top-k' lists ----
+    // ---- end of the launch (pass): fold both slots' rows into the per-query global top-k' lists ----
     __syncwarp();
 #pragma unroll 1
     for (int slot = 0; slot < 2; ++slot) {
@@ -402,8 +402,9 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         for (int i = lane; i < m; i += 32) buf[n + i] = ld_cg_entry(gl + i);
         __syncwarp();
         int tot = n + m;
+        uint32_t kth = 0;
         if (tot > k) {
-          warp_prune(buf, tot, k, my_hist);
+          kth = warp_prune(buf, tot, k, my_hist);
           tot = k;
           __syncwarp();
         }
@@ -412,6 +413,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         __syncwarp();
         if (lane == 0) {
           *reinterpret_cast<volatile uint32_t*>(&p.sink.qcnt[q]) = static_cast<uint32_t>(tot);
+          if (kth) atomicMax(&p.sink.tau_g[q], kth);  // exact k'-th best of everything folded so far: seeds the next pass
           __threadfence();
           atomicExch(&p.sink.lock[q], 0u);
         }

@@ -83,8 +83,10 @@ def test_stream_kernel(case, nq, store):
     n, d, k = case
     c, x = gen_inputs(n, d, nq, seed=200 + d)
     # 16-bit storage with more than one query goes to the tensor-core streaming kernel (K2T); K2 keeps nq = 1 and fp32 storage
-    run_and_check(c, x, k, store=store, path="auto", expect_path="stream" if (store == "f32" or nq == 1) else "tstream")
-    if store != "f32" and nq > 1:
+    # ... and single queries on long rows (>= 512 B), where it already sits on the HBM roofline
+    long_rows = (d + 63) // 64 * 64 * 2 >= 512
+    run_and_check(c, x, k, store=store, path="auto", expect_path="stream" if (store == "f32" or (nq == 1 and long_rows)) else "tstream")
+    if store != "f32":
         run_and_check(c, x, k, store=store, path="stream", expect_path="stream")
 
 
