@@ -35,6 +35,7 @@ CONFIGS = {
     # name: (Q, N, D, k, store dtype, normalised, description)
     "c1": (1000, 100_000, 384, 10, "f32", True, "C1: 1k q x 100k x 384 fp32 (BGE-small shape), top-10"),
     "c2": (6980, 8_800_000, 768, 100, "bf16", True, "C2: MS MARCO-passage shape, 6980 q x 8.8M x 768 bf16 corpus, top-100"),
+    "c2f": (6980, 8_800_000, 768, 100, "f32", True, "C2 shape with fp32 storage (the reference's own dtype): 6980 q x 8.8M x 768 fp32, top-100"),
     "c3": (100_000, 21_000_000, 1024, 100, "bf16", True, "C3: BGE-large shape, 100k q x 21M x 1024 bf16, top-100"),
     "c4": (50_000, 5_000_000, 1536, 10, "bf16", True, "C4: MMEB-style, 50k q x 5M x 1536, top-10"),
     "c5": (65_536, 10_000_000, 64, 500, "bf16", False, "C5: two-tower recsys, 65536 q x 10M x 64, top-500"),
@@ -319,21 +320,24 @@ def run_ours(a):
 
     peaks = load_peaks()
     path = st1["last_path_name"]
-    if path == "stream":
+    hbm_bound = path in ("stream", "tstream")
+    if hbm_bound:
         esz = 4 if store == "f32" else 2
         bytes_per_launch = (hi - lo) * ((D + 63) // 64 * 64) * esz
         achieved = bytes_per_launch / (kern_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "traffic": None}
     else:
-        flops = 2.0 * Q * (hi - lo) * D
+        # a step is ceil(Q / batch) launches of the same kernel over the whole shard: average work per launch
+        launches_per_step = max(st1["main_kernel_count"], 1) / a.steps
+        flops = 2.0 * Q * (hi - lo) * D / launches_per_step
         achieved = flops / (kern_ms * 1e-3) / 1e12
         peak = peaks["bf16_tflops_sustained"]
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                 "frac_of_nominal_2250": achieved / 2250.0}
-    roof.update({"kernel": {"tensor": "k1_search_kernel", "stream": "k2_stream_kernel", "exact": "kx_search_kernel"}.get(path, path),
+    roof.update({"kernel": {"tensor": "k1_search_kernel", "stream": "k2_stream_kernel", "tstream": "k2t_stream_kernel", "exact": "kx_search_kernel"}.get(path, path),
                  "kernel_ms": kern_ms, "kernel_launches_timed": st1["main_kernel_count"], "peak_source": peaks["source"],
-                 "algorithmic_work": "2*Q*(N/G)*D FLOPs per launch" if path != "stream" else "N*ld*sizeof(T) bytes per launch"})
+                 "algorithmic_work": "2*Q*(N/G)*D FLOPs per launch" if not hbm_bound else "N*ld*sizeof(T) bytes per launch"})
 
     cpu = None
     if world == 1 and not a.no_cpu_baseline:

@@ -44,6 +44,10 @@ struct nxf_index {
   int64_t n = 0, capacity = 0;
   void* data = nullptr;    // [capacity, ld] of store_dtype
   float* half_norm = nullptr;  // [capacity] 0.5*|row|^2 (L2 only)
+  // fp32 storage only: the rows again as two bf16 planes [hi | mid] per row, the operand of the tensor-core path (built on first use)
+  void* split = nullptr;       // [split_cap + 256, 2 * ld] bf16
+  int64_t split_cap = 0, split_rows = 0;  // rows allocated / rows converted so far
+  bool split_failed = false;   // the shadow did not fit in device memory: stay on the FFMA kernel until the storage changes
   int64_t id_offset = 0;
   int sm_count = 0;
   int cc_major = 0;
@@ -119,10 +123,40 @@ int ensure_capacity(nxf_index* idx, int64_t want, cudaStream_t stream) {
   }
   if (idx->data) cudaFree(idx->data);
   if (idx->half_norm) cudaFree(idx->half_norm);
+  if (idx->split) cudaFree(idx->split);
+  idx->split = nullptr; idx->split_cap = 0; idx->split_rows = 0; idx->split_failed = false;
   idx->data = nd;
   idx->half_norm = nh;
   idx->capacity = cap;
   idx->stats.storage_bytes = static_cast<int64_t>((cap + 256) * idx->ld * esz);
+  return NXF_OK;
+}
+
+// fp32 storage: bring the two-plane bf16 shadow up to date with the stored rows.  Returns NXF_ENOMEM (and remembers it) when the
+// shadow does not fit; the caller then stays on the FFMA kernel.
+int ensure_split(nxf_index* idx, cudaStream_t stream) {
+  if (idx->split_failed) return NXF_ENOMEM;
+  if (idx->split_cap < idx->capacity) {
+    if (idx->split) { cudaFree(idx->split); idx->split = nullptr; idx->split_cap = 0; idx->split_rows = 0; }
+    const size_t bytes = static_cast<size_t>(idx->capacity + 256) * idx->ld * 2 * sizeof(uint16_t);
+    cudaError_t e = cudaMalloc(&idx->split, bytes);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      idx->split = nullptr;
+      idx->split_failed = true;
+      return NXF_ENOMEM;
+    }
+    idx->split_cap = idx->capacity;
+    idx->stats.storage_bytes += static_cast<int64_t>(bytes);
+  }
+  if (idx->split_rows < idx->n) {
+    const float* src = static_cast<const float*>(idx->data) + static_cast<size_t>(idx->split_rows) * idx->ld;
+    uint16_t* dst = static_cast<uint16_t*>(idx->split) + static_cast<size_t>(idx->split_rows) * idx->ld * 2;
+    int rc = launch_split_rows(src, idx->ld, dst, idx->n - idx->split_rows, stream);
+    if (rc) return rc;
+    idx->stats.kernel_launches++;
+    idx->split_rows = idx->n;
+  }
   return NXF_OK;
 }
 
@@ -213,6 +247,7 @@ void nxf_destroy(nxf_index* idx) {
     DeviceGuard g(idx->device);
     if (idx->data) cudaFree(idx->data);
     if (idx->half_norm) cudaFree(idx->half_norm);
+    if (idx->split) cudaFree(idx->split);
     if (idx->scratch) cudaFree(idx->scratch);
     if (idx->pinned) cudaFreeHost(idx->pinned);
   }
@@ -223,6 +258,7 @@ int nxf_reset(nxf_index* idx) {
   NXF_REQUIRE(idx != nullptr, "nxf_reset: NULL index");
   std::lock_guard<std::mutex> lk(idx->mu);
   idx->n = 0;
+  idx->split_rows = 0;
   return NXF_OK;
 }
 
@@ -407,6 +443,7 @@ struct SearchPlan {
   int k_eff = 0;     // min(k, n)
   int k_fetch = 0;   // per-owner keep count in the main kernel
   int rescore = 0;
+  int split = 0;     // K1 over the two-plane bf16 shadow of fp32 rows
   int cap = 0;
   int grid = 0;
   int num_qt = 0, chunks = 1;
@@ -423,9 +460,10 @@ struct SearchPlan {
 
 }  // namespace
 
-static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int flags, SearchPlan* sp) {
+static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int flags, bool split_ok, SearchPlan* sp) {
   SearchPlan& P = *sp;
   const bool store16 = idx->store_dtype != NXF_F32;
+  const bool tens = store16 || split_ok;  // K1 can run: 16-bit rows, or fp32 rows with their bf16 shadow
   P.k_eff = static_cast<int>(std::min<int64_t>(k, idx->n));
   int path;
   if (flags & NXF_SEARCH_FORCE_EXACT) path = NXF_PATH_EXACT;
@@ -438,7 +476,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
            nq >= env_int("NXF_TSTREAM_MIN_NQ", idx->ld * dtype_size(idx->store_dtype) < 512 ? 1 : 2))
     path = NXF_PATH_TSTREAM;
   else if (nq <= NXF_STREAM_MAX_NQ) path = NXF_PATH_STREAM;
-  else path = store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
+  else path = tens ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
 
   const int64_t row_bytes = idx->ld * dtype_size(idx->store_dtype);
   if (path == NXF_PATH_TSTREAM) {
@@ -452,7 +490,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
                   (long long)nq, idx->dim);
         return NXF_EUNSUPPORTED;
       }
-      path = nq <= NXF_STREAM_MAX_NQ ? NXF_PATH_STREAM : (store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT);
+      path = nq <= NXF_STREAM_MAX_NQ ? NXF_PATH_STREAM : (tens ? NXF_PATH_TENSOR : NXF_PATH_EXACT);
     } else {
       P.stages = st;
       P.nq_t = nq_pad;
@@ -467,17 +505,18 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     while (stages > 1 && k2_smem_bytes(idx->ld, dtype_size(idx->store_dtype), nq_t, rw, stages) > 200 * 1024) --stages;
     if (stages < 2) {
       if (flags & NXF_SEARCH_FORCE_STREAM) { set_error("nxf_search: rows of %lld bytes are too long for the stream kernel", (long long)row_bytes); return NXF_EUNSUPPORTED; }
-      path = store16 ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
+      path = tens ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
     } else {
       P.rw = rw; P.nq_t = nq_t; P.stages = stages;
       P.k2_smem = k2_smem_bytes(idx->ld, dtype_size(idx->store_dtype), nq_t, rw, stages);
     }
   }
-  if (path == NXF_PATH_TENSOR && !store16) {
-    set_error("nxf_search: the tensor-core path needs f16/bf16 storage (index stores f32)");
+  if (path == NXF_PATH_TENSOR && !tens) {
+    set_error("nxf_search: the tensor-core path over f32 storage needs its bf16 shadow, which did not fit in device memory (or NXF_F32_TENSOR=0)");
     return NXF_EUNSUPPORTED;
   }
   P.path = path;
+  P.split = (path == NXF_PATH_TENSOR && !store16) ? 1 : 0;
   P.k_fetch = P.k_eff;
   P.rescore = 0;
   if (path == NXF_PATH_STREAM) {
@@ -522,7 +561,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.cta_group = cg;
     // the MMA rounds the queries to the storage type: over-fetch and re-score in fp32 unless the
     // caller's queries already are of that type (or asked not to)
-    const bool q_exact = (q_dtype == idx->store_dtype);
+    const bool q_exact = !P.split && (q_dtype == idx->store_dtype);
     if (!(flags & NXF_SEARCH_NO_RESCORE) && !q_exact) {
       P.rescore = 1;
       // over-fetch k' = k + max(16, k/4): the bf16 rounding of a unit query perturbs a score by ~6e-5 (1 sigma) while
@@ -599,12 +638,22 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     // device outputs: run the arena merge over an all-empty arena (qcnt = 0)
   }
 
+  // fp32 storage: batches beyond the stream kernel's go to the tensor cores over the bf16 [hi | mid] shadow of the rows, built here
+  // on first use (NXF_F32_TENSOR=0 keeps them on the FFMA kernel)
+  bool split_ok = false;
+  if (idx->store_dtype == NXF_F32 && idx->n > 0 && !(flags & (NXF_SEARCH_FORCE_EXACT | NXF_SEARCH_FORCE_STREAM | NXF_SEARCH_FORCE_TSTREAM)) &&
+      ((flags & NXF_SEARCH_FORCE_TENSOR) || (nq > NXF_STREAM_MAX_NQ && env_int("NXF_F32_TENSOR", 1) != 0))) {
+    rc = ensure_split(idx, stream);
+    if (rc == NXF_OK) split_ok = true;
+    else if (rc != NXF_ENOMEM) return rc;
+  }
+
   // plan; if the per-query arena forces several launches, re-plan for the launch size
   SearchPlan P;
   int64_t batch = nq;
   for (int it = 0; it < 8; ++it) {
     P = SearchPlan();
-    rc = plan_search(idx, batch, q_dtype, k, flags, &P);
+    rc = plan_search(idx, batch, q_dtype, k, flags, split_ok, &P);
     if (rc) return rc;
     if (idx->n == 0) break;
     if (P.path == NXF_PATH_STREAM) { batch = std::min<int64_t>(nq, P.batch); break; }
@@ -630,7 +679,8 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     Carver cv(base);
     q_src = q_on_device ? nullptr : cv.take<unsigned char>(static_cast<size_t>(batch) * q_ld * qsz);
     q_f32 = cv.take<float>(static_cast<size_t>(nq_pad) * idx->ld);
-    q16 = (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld) : nullptr;
+    q16 = (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld * (P.split ? 2 : 1))
+                                                                    : nullptr;
     tau_g = cv.take<uint32_t>(static_cast<size_t>(3 * nq_pad + 64));  // tau | qcnt | lock | K1 round counter
     qcnt = tau_g ? tau_g + nq_pad : nullptr;
     qlock = tau_g ? tau_g + 2 * nq_pad : nullptr;
@@ -659,7 +709,11 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     rc = launch_convert_rows(q_dev, q_dtype, q_ld, q_f32, NXF_F32, idx->ld, bn, idx->dim, stream);
     if (rc) return rc;
     idx->stats.kernel_launches++;
-    if (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) {
+    if (P.split) {
+      rc = launch_split_rows(q_f32, idx->ld, q16, bn, stream);
+      if (rc) return rc;
+      idx->stats.kernel_launches++;
+    } else if (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) {
       rc = launch_convert_rows(q_dev, q_dtype, q_ld, q16, idx->store_dtype, idx->ld, bn, idx->dim, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
@@ -716,6 +770,8 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     } else if (P.path == NXF_PATH_TENSOR) {
       K1Params kp;
       kp.n = idx->n; kp.nq = bn; kp.kblocks = static_cast<int>(idx->ld / 64);
+      kp.split_kb = 0;
+      if (P.split) { kp.split_kb = kp.kblocks; kp.kblocks *= 3; }
       kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group));
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
@@ -748,7 +804,8 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       for (int ps = 0; ps < n_pass; ++ps) {
         kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
         kp.sync_ctr = tau_g + 3 * nq_pad + ps;   // one round counter per pass (all zeroed above)
-        rc = launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
+        rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
+                     : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
         if (rc) return rc;
         idx->stats.kernel_launches++;
       }

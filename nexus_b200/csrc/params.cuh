@@ -25,7 +25,9 @@ struct KxParams {
 struct K1Params {
   int64_t n;    // corpus rows
   int64_t nq;   // query rows
-  int kblocks;  // ld / 64
+  int kblocks;  // K blocks of 64 elements accumulated per tile: ld / 64, or 3 * split_kb
+  int split_kb; // 0, or (fp32 storage as two bf16 planes [hi | mid] per row, each split_kb blocks wide) the plane width: the three
+                // segments of a tile are (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
   int num_qt;   // query tiles of 128*CG rows (<= number of clusters)
   int64_t tile_begin, tile_end;  // corpus tiles [begin, end) of this pass (a search is 1-3 passes: seed, seed, rest)
   int round_tiles;     // corpus tiles per round (the L2-resident window)
@@ -108,6 +110,7 @@ int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, c
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,
                         cudaStream_t stream);
+int launch_split_rows(const float* src, int64_t ld, void* dst, int64_t n, cudaStream_t stream);
 int launch_half_norm(const void* rows, int dtype, int64_t ld, int64_t n, int dim, float* out, cudaStream_t stream);
 int launch_pool(const void* hidden, int h_dtype, const int64_t* mask, int64_t B, int64_t L, int64_t H, int pooling, int normalize,
                 float eps, void* out, int out_dtype, cudaStream_t stream);

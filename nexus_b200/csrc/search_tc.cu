@@ -200,16 +200,23 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           for (int64_t t = r0 + lo; t < r0 + hi; ++t) {
             const int32_t c_row0 = static_cast<int32_t>(t * BLOCK_N + rank * C::LOAD_N);
             for (int kb = 0; kb < p.kblocks; ++kb) {
+              // column (in elements) of this K block in the query / corpus rows; split storage walks (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
+              int32_t q_col = kb * BLOCK_K, c_col = kb * BLOCK_K;
+              if (p.split_kb > 0) {
+                const int seg = kb / p.split_kb, w = kb - seg * p.split_kb;
+                q_col = ((seg == 2 ? p.split_kb : 0) + w) * BLOCK_K;
+                c_col = ((seg == 1 ? p.split_kb : 0) + w) * BLOCK_K;
+              }
               mbar_wait(&empty[s], ph ^ 1);
               if (p.debug & 4) {  // pipeline timing only: no loads, the MMAs run on whatever the ring holds
                 if (CG == 1 || rank == 0) mbar_arrive(&full[s]); else mbar_arrive_cluster(&full[s], 0);
               } else if (CG == 1) {
                 mbar_expect_tx(&full[s], C::STAGE_BYTES);
-                tma_load_2d(&tmap_q, &full[s], a_ptr(s), kb * BLOCK_K, q_row0, kEvictLast);
-                tma_load_2d(&tmap_c, &full[s], b_ptr(s), kb * BLOCK_K, c_row0, kEvictNormal);
+                tma_load_2d(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
+                tma_load_2d(&tmap_c, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
               } else {
-                tma_load_2d_2sm(&tmap_q, &full[s], a_ptr(s), kb * BLOCK_K, q_row0, kEvictLast);
-                tma_load_2d_2sm(&tmap_c, &full[s], b_ptr(s), kb * BLOCK_K, c_row0, kEvictNormal);
+                tma_load_2d_2sm(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
+                tma_load_2d_2sm(&tmap_c, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
                 if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
                 else mbar_arrive_cluster(&full[s], 0);
               }

@@ -128,6 +128,45 @@ def test_tensor_kernel_rescored(case, store):
     run_and_check(c, x, k, store=store, path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
 
 
+@pytest.mark.parametrize("case", CASES + [(60000, 384, 700, 100), (30000, 1024, 300, 10)])
+def test_tensor_kernel_fp32_storage(case):
+    """fp32 rows on tcgen05: the rows' bf16 [hi | mid] shadow, three MMA segments per tile (q_hi c_hi + q_hi c_mid + q_mid c_hi),
+    over-fetch and fp32 re-score.  Default dispatch above the stream kernel's batch; results to the fp32 tolerance."""
+    n, d, q, k = case
+    c, x = gen_inputs(n, d, q, seed=600 + n % 71)
+    run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, expect_path="tensor" if q > 4 else "stream")
+    run_and_check(c, x, k, store="f32", path="tensor", rtol=1e-5, expect_path="tensor")
+    # without the re-score the scores are the three-product sums themselves: 2^-16 per term
+    run_and_check(c, x, k, store="f32", path="tensor_raw", rtol=2e-5, atol=4e-6, expect_path="tensor", min_recall=0.999)
+
+
+def test_tensor_fp32_storage_follows_adds_and_reset():
+    """The shadow is built on first use and extended / rebuilt when rows are added, the storage grows or the index is reset."""
+    from nexus_b200 import FlatIndex
+    c, x = gen_inputs(9000, 200, 64, seed=31)
+    idx = FlatIndex(200, "ip", "f32")
+    idx.add(c[:2000])
+    for upto in (2000, 2500, 9000):
+        if idx.ntotal < upto:
+            idx.add(c[idx.ntotal:upto])
+        D, I = idx.search(x, 20)
+        assert idx.stats()["last_path_name"] == "tensor"
+        ref_s, ref_i = oracle.blocked_ip_search(c[:upto], x, 20, pad=True)
+        rep = oracle.check_topk(ref_s, ref_i, D, I, c[:upto], x, rtol=1e-5)
+        assert rep.ok, (upto, rep.messages[:5])
+    idx.reset()
+    idx.add(c[5000:6000])
+    D, I = idx.search(x, 20)
+    ref_s, ref_i = oracle.blocked_ip_search(c[5000:6000], x, 20, pad=True)
+    rep = oracle.check_topk(ref_s, ref_i, D, I, c[5000:6000], x, rtol=1e-5)
+    assert rep.ok, rep.messages[:5]
+
+
+def test_tensor_fp32_storage_l2():
+    c, x = gen_inputs(20000, 128, 200, seed=41, normalize=False)
+    run_and_check(c, x, 50, store="f32", path="auto", metric="l2", rtol=2e-4, atol=1e-3, expect_path="tensor", min_recall=0.999)
+
+
 def test_tensor_default_dispatch_and_bf16_recall_vs_fp32():
     """BASELINE bar: bf16 recall@k >= 0.999 against the fp32 reference on the same (bf16-valued) corpus."""
     c, x = gen_inputs(50000, 768, 512, seed=77)
@@ -238,4 +277,6 @@ def test_errors_are_loud():
     with pytest.raises(ValueError):
         idx.search(np.zeros((1, 16), np.float32), 5000)
     with pytest.raises(Exception):
-        idx.search(np.zeros((9, 16), np.float32), 2, flags=FLAGS["tensor"])   # f32 storage has no tensor path
+        idx.search(np.zeros((9, 16), np.float32), 2, flags=FLAGS["tstream"])  # f32 storage has no tensor stream kernel
+    with pytest.raises(Exception):
+        idx.search(np.zeros((9, 16), np.float32), 2, flags=FLAGS["tensor"] | FLAGS["exact"])   # two forced paths
