@@ -444,6 +444,7 @@ struct SearchPlan {
   int k_fetch = 0;   // per-owner keep count in the main kernel
   int rescore = 0;
   int split = 0;     // K1 over the two-plane bf16 shadow of fp32 rows
+  int seed = 0;      // K2T: threshold-seeding pass over the first tile of every CTA
   int cap = 0;
   int grid = 0;
   int num_qt = 0, chunks = 1;
@@ -475,6 +476,9 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
   else if (store16 && nq <= NXF_TSTREAM_MAX_NQ &&
            nq >= env_int("NXF_TSTREAM_MIN_NQ", idx->ld * dtype_size(idx->store_dtype) < 512 ? 1 : 2))
     path = NXF_PATH_TSTREAM;
+  // fp32 rows: K2 keeps up with HBM for one query (78 % at two); from two on the shadow planes go through K2T
+  else if (split_ok && nq <= NXF_TSTREAM_MAX_NQ && nq >= env_int("NXF_TSTREAM_MIN_NQ_F32", 2))
+    path = NXF_PATH_TSTREAM;
   else if (nq <= NXF_STREAM_MAX_NQ) path = NXF_PATH_STREAM;
   else path = tens ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
 
@@ -483,10 +487,11 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     // K2T keeps the (16-padded) queries resident in shared memory; if that leaves fewer than 4 ring stages, or the storage is
     // fp32, fall back to the kernels that do not need it
     const int nq_pad = static_cast<int>(round_up64(std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ), 16));
-    const int st = store16 ? k2t_plan_stages(static_cast<int>(idx->ld / 64), nq_pad) : 0;
+    const int st = store16 ? k2t_plan_stages(static_cast<int>(idx->ld / 64), nq_pad)
+                           : (split_ok ? k2t_plan_stages(static_cast<int>(2 * idx->ld / 64), nq_pad) : 0);
     if (st == 0) {
       if (flags & NXF_SEARCH_FORCE_TSTREAM) {
-        set_error("nxf_search: the tensor stream kernel needs f16/bf16 storage and queries that fit in shared memory (nq=%lld, dim=%d)",
+        set_error("nxf_search: the tensor stream kernel needs queries that fit in shared memory (nq=%lld, dim=%d) and, for f32 storage, the bf16 shadow",
                   (long long)nq, idx->dim);
         return NXF_EUNSUPPORTED;
       }
@@ -516,7 +521,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     return NXF_EUNSUPPORTED;
   }
   P.path = path;
-  P.split = (path == NXF_PATH_TENSOR && !store16) ? 1 : 0;
+  P.split = ((path == NXF_PATH_TENSOR || path == NXF_PATH_TSTREAM) && !store16) ? 1 : 0;
   P.k_fetch = P.k_eff;
   P.rescore = 0;
   if (path == NXF_PATH_STREAM) {
@@ -529,7 +534,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.batch = P.nq_t;
   } else if (path == NXF_PATH_TSTREAM) {
     // same query-side rounding as K1: over-fetch and re-score in fp32 unless the queries already are of the storage type
-    if (!(flags & NXF_SEARCH_NO_RESCORE) && q_dtype != idx->store_dtype) {
+    if (!(flags & NXF_SEARCH_NO_RESCORE) && (P.split || q_dtype != idx->store_dtype)) {
       P.rescore = 1;
       int64_t kf = static_cast<int64_t>(P.k_eff) + std::max<int64_t>(16, (P.k_eff + 3) / 4);
       kf = (kf + 7) / 8 * 8;
@@ -538,9 +543,16 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.n_tiles = ceil_div64(idx->n, 128);
     P.grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(idx->sm_count, P.n_tiles)));
     // overflow checks every `ce` tiles: short rows (few K blocks per tile) cannot afford a barrier per tile
-    P.rw = std::max(1, std::min(8, 16 / std::max<int>(1, static_cast<int>(idx->ld / 64))));
+    P.rw = std::max(1, std::min(8, 16 / std::max<int>(1, static_cast<int>(idx->ld / 64) * (P.split ? 2 : 1))));
     P.cap = 2 * P.k_fetch + 2 * 128 * P.rw;   // pruned once more than 2k' entries are held
     P.owners = static_cast<int64_t>(P.grid) * P.nq_t;
+    // threshold seeding (DESIGN.md "K2T"): one tile per CTA first, whole lists (<= 128 entries) into the arena, the sample's k'-th best
+    // into tau_g; pays off once every CTA streams many tiles (NXF_K2T_SEED=0/1 overrides)
+    // measured (C5, D = 64): the two extra launches cost ~0.1 ms and pay for themselves from nq * k' ~ 800 on (NXF_K2T_SEED=0/1 overrides)
+    {
+      const int seed_env = env_int("NXF_K2T_SEED", -1);
+      P.seed = seed_env >= 0 ? seed_env != 0 : (nq * static_cast<int64_t>(P.k_fetch) >= 768);
+    }
     P.arena_stride = static_cast<int64_t>(P.grid) * P.k_fetch;
     P.batch = std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ);
   } else if (path == NXF_PATH_EXACT) {
@@ -597,7 +609,8 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       }
     }
     P.chunks = static_cast<int>(ceil_div64(std::max<int64_t>(P.n_tiles, 1), P.round_tiles));  // reported as "chunks": rounds per launch
-    P.cap = 2 * P.k_fetch + 256;  // pruned between tiles once fewer than 256 (one tile of appends) slots are left
+    // pruned between tiles once fewer than 256 (one tile of appends) slots are left
+    P.cap = std::max(2, env_int("NXF_K1_CAP_MULT", 2)) * P.k_fetch + 256;
     P.owners = static_cast<int64_t>(P.grid) * 128 * 2;  // two query-tile slots per CTA
     P.arena_stride = P.k_fetch;  // K1 folds every owner's candidates into ONE list of k' per query (merged under a lock)
   }
@@ -641,8 +654,9 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   // fp32 storage: batches beyond the stream kernel's go to the tensor cores over the bf16 [hi | mid] shadow of the rows, built here
   // on first use (NXF_F32_TENSOR=0 keeps them on the FFMA kernel)
   bool split_ok = false;
-  if (idx->store_dtype == NXF_F32 && idx->n > 0 && !(flags & (NXF_SEARCH_FORCE_EXACT | NXF_SEARCH_FORCE_STREAM | NXF_SEARCH_FORCE_TSTREAM)) &&
-      ((flags & NXF_SEARCH_FORCE_TENSOR) || (nq > NXF_STREAM_MAX_NQ && env_int("NXF_F32_TENSOR", 1) != 0))) {
+  if (idx->store_dtype == NXF_F32 && idx->n > 0 && !(flags & (NXF_SEARCH_FORCE_EXACT | NXF_SEARCH_FORCE_STREAM)) &&
+      ((flags & (NXF_SEARCH_FORCE_TENSOR | NXF_SEARCH_FORCE_TSTREAM)) ||
+       (nq >= env_int("NXF_TSTREAM_MIN_NQ_F32", 2) && env_int("NXF_F32_TENSOR", 1) != 0))) {
     rc = ensure_split(idx, stream);
     if (rc == NXF_OK) split_ok = true;
     else if (rc != NXF_ENOMEM) return rc;
@@ -673,7 +687,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   const size_t qsz = dtype_size(q_dtype);
   unsigned char* base = nullptr;
   float* q_f32 = nullptr; void* q16 = nullptr; void* q_src = nullptr; uint32_t* tau_g = nullptr; uint32_t* qcnt = nullptr; uint32_t* qlock = nullptr;
-  Entry* arena = nullptr; Entry* cand = nullptr; float* o_scores = nullptr; int64_t* o_ids = nullptr;
+  Entry* arena = nullptr; Entry* cand = nullptr; float* o_scores = nullptr; int64_t* o_ids = nullptr; uint32_t* k2t_cnt = nullptr;
   const int64_t nq_pad = round_up64(batch, 256);
   for (int pass = 0; pass < 2; ++pass) {
     Carver cv(base);
@@ -686,6 +700,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     qlock = tau_g ? tau_g + 2 * nq_pad : nullptr;
     arena = cv.take<Entry>(static_cast<size_t>(batch) * P.arena_stride);
     cand = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(P.owners, 1)) * P.cap);
+    k2t_cnt = P.path == NXF_PATH_TSTREAM ? cv.take<uint32_t>(static_cast<size_t>(std::max<int64_t>(P.owners, 1))) : nullptr;
     if (!out_on_device) {
       o_scores = cv.take<float>(static_cast<size_t>(batch) * k);
       o_ids = cv.take<int64_t>(static_cast<size_t>(batch) * k);
@@ -747,6 +762,8 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     } else if (P.path == NXF_PATH_TSTREAM) {
       K2TParams kp;
       kp.n = idx->n; kp.nq = static_cast<int>(bn); kp.nq_pad = static_cast<int>(round_up64(bn, 16)); kp.kblocks = static_cast<int>(idx->ld / 64);
+      kp.split_kb = 0;
+      if (P.split) { kp.split_kb = kp.kblocks; kp.kblocks *= 2; }
       kp.stages = k2t_plan_stages(kp.kblocks, kp.nq_pad);
       kp.tbuf_stride = kp.nq_pad <= 32 ? 32 : (kp.nq_pad <= 64 ? 64 : 128);
       kp.tbufs = std::min(8, 512 / kp.tbuf_stride);
@@ -754,8 +771,37 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.check_every = P.rw;
       kp.sink = sink;
       kp.sink.cap = P.cap;
-      // the candidate buffers are laid out [cta][nq_pad of THIS launch][cap]; the plan sized them for the largest launch
-      rc = launch_k2t(idx->store_dtype, q16, bn, idx->data, idx->ld, kp, P.grid, stream);
+      const void* c_rows = P.split ? idx->split : idx->data;
+      const int64_t c_ld = P.split ? 2 * idx->ld : idx->ld;
+      const int c_dt = P.split ? NXF_BF16 : idx->store_dtype;
+      // Threshold seeding: up to two short launches first (one tile per CTA, then 16 more), each followed by the seed kernel, which
+      // raises tau_g to the k'-th best over ALL lists of the query; the last launch streams the rest with that threshold.
+      int64_t bounds[4] = {0, 0, 0, P.n_tiles};
+      int n_pass = 0;
+      if (P.seed) {
+        const int64_t g = P.grid;
+        int64_t prev = 0;
+        const int64_t cuts[2] = {g, 17 * g};
+        for (int c = 0; c < 2; ++c) {
+          // a cut is worth a launch when it leaves at least 4x as much behind it, and its sample holds well over k' rows
+          if (4 * cuts[c] <= P.n_tiles && cuts[c] * 128 >= 8 * static_cast<int64_t>(P.k_fetch)) { bounds[++n_pass] = cuts[c]; prev = cuts[c]; }
+        }
+        (void)prev;
+      }
+      bounds[++n_pass] = P.n_tiles;
+      kp.cnt_g = k2t_cnt;
+      for (int ps = 0; ps + 1 < n_pass; ++ps) {
+        kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
+        kp.first_pass = ps == 0; kp.last_pass = 0; kp.no_check = (bounds[ps + 1] - bounds[ps] <= P.grid) ? 1 : 0;
+        rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
+        if (rc) return rc;
+        rc = launch_seed_tau_lists(cand, k2t_cnt, P.grid, kp.nq_pad, P.cap, P.k_fetch, tau_g, static_cast<int>(bn), stream);
+        if (rc) return rc;
+        idx->stats.kernel_launches += 2;
+      }
+      kp.tile_begin = bounds[n_pass - 1]; kp.tile_end = P.n_tiles;
+      kp.first_pass = n_pass == 1; kp.last_pass = 1; kp.no_check = 0;
+      rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
     } else if (P.path == NXF_PATH_EXACT) {
@@ -804,6 +850,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       for (int ps = 0; ps < n_pass; ++ps) {
         kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
         kp.sync_ctr = tau_g + 3 * nq_pad + ps;   // one round counter per pass (all zeroed above)
+        kp.prof = tau_g + 3 * nq_pad + 16;
         rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
                      : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
         if (rc) return rc;
@@ -811,6 +858,13 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       }
     }
 
+    if (P.path == NXF_PATH_TENSOR && (env_int("NXF_K1_DEBUG", 0) & 32)) {
+      unsigned long long h[4] = {0, 0, 0, 0};
+      NXF_CUDA(cudaMemcpyAsync(h, tau_g + 3 * nq_pad + 16, sizeof(h), cudaMemcpyDeviceToHost, stream));
+      NXF_CUDA(cudaStreamSynchronize(stream));
+      fprintf(stderr, "[nxf K1 prof] prunes=%llu prune_cycles/warp=%.0f end_merge_cycles/warp=%.0f cycles/prune=%.0f (epilogue warps %llu)\n", h[0],
+              h[3] ? double(h[1]) / h[3] : 0.0, h[3] ? double(h[2]) / h[3] : 0.0, h[0] ? double(h[1]) / h[0] : 0.0, h[3]);
+    }
     if (pe0) {
       NXF_CUDA(cudaEventRecord(pe1, stream));
       idx->prof_events.emplace_back(pe0, pe1);

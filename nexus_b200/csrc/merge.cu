@@ -234,6 +234,103 @@ int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, c
 }
 
 
+// ---- threshold seeding -------------------------------------------------------------------------
+// K2T keeps one candidate list per (CTA, query); a CTA's own k'-th best only reflects 1/grid of the corpus, so its threshold
+// is weak.  Between two launches of a search this kernel looks at ALL lists of a query (one CTA per query): gathers their
+// keys into shared memory, selects the k'-th largest and raises tau_g to it.  That is a valid lower bound on the final k'-th
+// score (k' held entries reach it), and it reflects every row streamed so far: the next launch rejects all but
+// ~k' * (rows of the launch / rows before it) scores per query.  The lists are not modified.
+constexpr int SEED_MAX_KEYS = 48 * 1024;  // 192 KB of shared memory; more candidates than that: the threshold is left as it is
+
+__global__ void __launch_bounds__(mg::THREADS) seed_tau_lists_kernel(const Entry* __restrict__ cand, const uint32_t* __restrict__ cnt_g,
+                                                                     int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g) {
+  extern __shared__ uint32_t seed_smem[];
+  __shared__ uint32_t hist[256];
+  __shared__ int offs[256 + 1];  // grid <= 256 (one CTA per SM)
+  uint32_t* keys = seed_smem;
+  const int q = blockIdx.x;
+  const int tid = threadIdx.x;
+  if (tid < 32) {  // exclusive scan of the list lengths by one warp, 8 lists per lane
+    int c[8], sum = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int b = tid * 8 + j;
+      c[j] = b < grid ? min(static_cast<int>(cnt_g[static_cast<int64_t>(b) * nq_pad + q]), cap) : 0;
+      sum += c[j];
+    }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (tid >= o) incl += t;
+    }
+    int run = incl - sum;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { offs[tid * 8 + j] = run; run += c[j]; }
+    if (tid == 31) offs[256] = incl;
+  }
+  __syncthreads();
+  const int total = offs[256];
+  if (total < k_fetch || total > SEED_MAX_KEYS) return;  // uniform per block
+  // gather: warp w copies the keys of lists w, w + 8, ... (independent coalesced loads, no index search)
+  const int warp = tid >> 5, lane = tid & 31;
+  uint32_t lmin = 0xFFFFFFFFu, lmax = 0u;
+  for (int b = warp; b < grid; b += mg::THREADS / 32) {
+    const int o = offs[b], c = offs[b + 1] - o;
+    const Entry* __restrict__ src = cand + (static_cast<int64_t>(b) * nq_pad + q) * cap;
+    for (int i = lane; i < c; i += 32) {
+      const uint32_t key = okey(src[i].score);
+      keys[o + i] = key;
+      lmin = min(lmin, key);
+      lmax = max(lmax, key);
+    }
+  }
+  lmin = __reduce_min_sync(0xFFFFFFFFu, lmin);
+  lmax = __reduce_max_sync(0xFFFFFFFFu, lmax);
+  uint32_t* red = hist;  // [2][8] counts, then min / max
+  if (lane == 0) { red[32 + warp] = lmin; red[48 + warp] = lmax; }
+  __syncthreads();
+  lmin = 0xFFFFFFFFu; lmax = 0u;
+#pragma unroll
+  for (int w = 0; w < mg::THREADS / 32; ++w) { lmin = min(lmin, red[32 + w]); lmax = max(lmax, red[48 + w]); }
+  // bitwise descent below the common prefix of min and max (select.cuh), counts reduced over the block; all threads track T
+  uint32_t T = lmax;
+  const uint32_t diff = lmin ^ lmax;
+  if (diff != 0u) {
+    const int top = 31 - __clz(diff);
+    T = (top == 31) ? 0u : (lmax & ~((2u << top) - 1u));
+    int par = 0;
+#pragma unroll 1
+    for (int b = top; b >= 0; --b, par ^= 1) {
+      const uint32_t c_key = T | (1u << b);
+      unsigned c = 0;
+      for (int i = tid; i < total; i += mg::THREADS) c += (keys[i] >= c_key) ? 1u : 0u;
+      c = __reduce_add_sync(0xFFFFFFFFu, c);
+      if (lane == 0) red[par * 8 + warp] = c;
+      __syncthreads();  // red[par] complete; red[par ^ 1] of the previous step is no longer read by anyone
+      unsigned tot = 0;
+#pragma unroll
+      for (int w = 0; w < mg::THREADS / 32; ++w) tot += red[par * 8 + w];
+      if (tot >= static_cast<unsigned>(k_fetch)) {
+        T = c_key;
+        if (tot == static_cast<unsigned>(k_fetch)) break;  // uniform: exactly k' keys >= T
+      }
+    }
+  }
+  if (tid == 0) atomicMax(&tau_g[q], T);
+}
+
+int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g, int nq,
+                          cudaStream_t stream) {
+  if (nq <= 0) return NXF_OK;
+  if (grid > 256) { set_error("seed: %d lists per query (max 256)", grid); return NXF_EUNSUPPORTED; }
+  const size_t smem = static_cast<size_t>(std::min<int64_t>(SEED_MAX_KEYS, static_cast<int64_t>(grid) * cap)) * sizeof(uint32_t);
+  NXF_CUDA(cudaFuncSetAttribute(seed_tau_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEED_MAX_KEYS * 4));
+  seed_tau_lists_kernel<<<static_cast<unsigned>(nq), mg::THREADS, smem, stream>>>(cand, cnt_g, grid, nq_pad, cap, k_fetch, tau_g);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
 // ---- multi-list merge (multi-GPU shard merge) ---------------------------------------------------
 __global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(MergeListsParams p) {
   __shared__ uint64_t keys[mg::MAXK];

@@ -34,6 +34,7 @@ struct K1Params {
   int sync_window;     // soft round barrier: a producer may run this many rounds ahead of the rest (0 = no barrier)
   uint32_t* sync_ctr;  // [1] zeroed per launch: rounds completed, summed over clusters
   const float* half_norm;
+  uint32_t* prof;      // debug bit5: 4 x uint64 {prunes, prune cycles, end-merge cycles, warps} summed over epilogue warps
   int debug;  // timing experiments: bit0 epilogue skips the selection; bit1 also skips the TMEM loads; bit2 producer issues no TMA;
               // bit3 issuer issues no MMA; bit4 epilogue computes the maxima but never appends
   SinkParams sink;
@@ -57,11 +58,19 @@ struct K2TParams {
   int64_t n;     // corpus rows
   int nq;        // queries (<= 128)
   int nq_pad;    // nq rounded up to 16 = UMMA N
-  int kblocks;   // ld / 64
+  int kblocks;   // 64-element K blocks per row (queries and corpus alike): ld / 64, or 2 * split_kb
+  int split_kb;  // 0, or (fp32 storage as bf16 planes [hi | mid]) blocks per plane: a c_hi block meets q_hi and q_mid, a c_mid block q_hi
   int stages;    // ring depth
   int tbufs;     // TMEM accumulator buffers
   int tbuf_stride;  // TMEM columns between buffers
   int check_every;  // tiles between two buffer-overflow checks (cap = 2k' + 2*128*check_every)
+  // a search is 1-3 launches over consecutive tile ranges (DESIGN.md "K2T, threshold seeding"); the per-(CTA, query) lists and
+  // their counts stay in global memory between launches
+  int64_t tile_begin, tile_end;  // this launch streams corpus tiles [tile_begin, tile_end), CTA b takes tile_begin + b + i * grid
+  uint32_t* cnt_g;  // [grid][nq_pad] list lengths carried from launch to launch
+  int first_pass;   // lists start empty
+  int last_pass;    // lists are reduced to k' and flushed to the arena at the end (else: lengths stored to cnt_g)
+  int no_check;     // one tile per CTA (<= 128 entries per list, below cap): skip the overflow checks
   const float* half_norm;
   SinkParams sink;
 };
@@ -106,6 +115,8 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* co
                cudaStream_t stream);
 size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages);
 int k2t_plan_stages(int kblocks, int nq_pad);
+int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g, int nq,
+                          cudaStream_t stream);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,

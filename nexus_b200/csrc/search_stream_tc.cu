@@ -81,21 +81,26 @@ __device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], int ch, floa
 #pragma unroll
   for (int j = 3; j < 15; j += 2) m = fmax3(m, d[j], d[j + 1]);
   m = fmaxf(m, d[15]);
-  if (m > 0.f && row_ok) {
+  const bool mine = m > 0.f && row_ok;
+  if (__any_sync(kFullMask, mine)) {  // warp-uniform: the whole (converged) epilogue warp takes the slow path together
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      if (d[j] > 0.f) {  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
-        const int qi = ch * 16 + j;
-        const int pos = atomicAdd(&cnt_s[qi], 1);
-        const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
-        cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
-        cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
+      const bool h = mine && d[j] > 0.f;  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
+      if (__any_sync(kFullMask, h)) {     // uniform: only the columns some row actually beats cost more than a vote
+        if (h) {
+          const int qi = ch * 16 + j;
+          const int pos = atomicAdd(&cnt_s[qi], 1);
+          const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
+          cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
+          cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
+        }
       }
     }
   }
 }
 
-template <bool BF16, bool L2>
+// W = accumulator columns per tcgen05.ld batch (16, 32 or 64): a tile's nq_pad columns are one or two batches
+template <bool BF16, bool L2, int W>
 __global__ void __launch_bounds__(k2t::THREADS, 1)
 k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K2TParams p) {
   using namespace k2t;
@@ -117,7 +122,8 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 
   const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
   const unsigned lane = lane_id();
-  const int64_t n_tiles = (p.n + BLOCK_M - 1) / BLOCK_M;
+  const int64_t t_first = p.tile_begin + blockIdx.x;  // this CTA's tiles: t_first, t_first + grid, ... < t_end
+  const int64_t t_end = p.tile_end;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
@@ -132,7 +138,8 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   if (warp == 2) tmem_alloc<1>(tmem_ptr_s, TMEM_COLS);
   if (threadIdx.x < MAX_NQ) {
     tau_s[threadIdx.x] = (static_cast<int>(threadIdx.x) < p.nq) ? tau_load(p.sink.tau_g, threadIdx.x) : INFINITY;  // padded columns accept nothing
-    cnt_s[threadIdx.x] = 0;
+    cnt_s[threadIdx.x] = (p.first_pass || static_cast<int>(threadIdx.x) >= p.nq)
+                             ? 0 : static_cast<int>(p.cnt_g[static_cast<int64_t>(blockIdx.x) * p.nq_pad + threadIdx.x]);
   }
   tc_fence_before();
   __syncthreads();
@@ -146,7 +153,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       for (int kb = 0; kb < p.kblocks; ++kb) tma_load_2d(&tmap_q, qfull, q_smem + kb * p.nq_pad * 128, kb * BLOCK_K, 0, kEvictLast);
       int s = 0;
       uint32_t ph = 0;
-      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      for (int64_t t = t_first; t < t_end; t += gridDim.x) {
         const int32_t row0 = static_cast<int32_t>(t * BLOCK_M);
         for (int kb = 0; kb < p.kblocks; ++kb) {
           mbar_wait(&empty[s], ph ^ 1);
@@ -166,7 +173,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       int s = 0;
       uint32_t ph = 0;
       uint32_t iter = 0;
-      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++iter) {
+      for (int64_t t = t_first; t < t_end; t += gridDim.x, ++iter) {
         const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
         mbar_wait(&tempty[b], bph ^ 1);
         tc_fence_after();
@@ -175,10 +182,17 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           mbar_wait(&full[s], ph);
           tc_fence_after();
           const uint64_t a_desc = umma_desc_sw128(smem_u32(ring + s * A_BYTES));
-          const uint64_t b_desc = umma_desc_sw128(smem_u32(q_smem + kb * p.nq_pad * 128));
+          // split storage: corpus block kb of the hi plane meets q_hi[kb] and q_mid[kb]; of the mid plane, q_hi[kb - split_kb]
+          const int qb = (p.split_kb > 0 && kb >= p.split_kb) ? kb - p.split_kb : kb;
+          const uint64_t b_desc = umma_desc_sw128(smem_u32(q_smem + qb * p.nq_pad * 128));
 #pragma unroll
           for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4)
             umma_f16<1>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, (kb | k4) != 0 ? 1u : 0u);
+          if (p.split_kb > 0 && kb < p.split_kb) {
+            const uint64_t b2_desc = umma_desc_sw128(smem_u32(q_smem + (kb + p.split_kb) * p.nq_pad * 128));
+#pragma unroll
+            for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) umma_f16<1>(d_tmem, a_desc + 2 * k4, b2_desc + 2 * k4, idesc, 1u);
+          }
           umma_commit<1>(&empty[s]);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
@@ -199,49 +213,56 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int chunks = p.nq_pad / 16;
     const int check_every = p.check_every;           // tiles between two overflow checks / threshold refreshes
     const int full_mark = cap - 2 * check_every * BLOCK_M;  // == 2k': see the margin note below
-    uint32_t iter = 0;
     int since_check = 0;
     float tau_next = (et < p.nq) ? tau_load(p.sink.tau_g, et) : INFINITY;
 
-    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++iter) {
-      const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
+    // The tile's accumulator is read in `batches` tcgen05.ld batches of W columns.  tcgen05.wait::ld waits for every outstanding
+    // load of the thread, so the software pipeline is two batches deep over the flat sequence of (tile, batch) units: while
+    // unit u is filtered, the load of unit u + 1 -- possibly the next tile's first batch -- is in flight.
+    constexpr int NB = W / 16;
+    const uint32_t batches = static_cast<uint32_t>((p.nq_pad + W - 1) / W);
+    const uint32_t n_it = t_first < t_end ? static_cast<uint32_t>((t_end - t_first + gridDim.x - 1) / gridDim.x) : 0u;
+    const uint32_t n_units = n_it * batches;
+
+    auto issue = [&](uint32_t u, uint32_t (&v)[W]) {
+      const uint32_t it = u / batches, bt = u - it * batches;
+      const uint32_t b = it % p.tbufs, bph = (it / p.tbufs) & 1;
+      if (bt == 0) {
+        mbar_wait(&tfull[b], bph);
+        tc_fence_after();
+      }
+      const uint32_t tb = taddr + b * p.tbuf_stride + bt * W;
+#pragma unroll
+      for (int i = 0; i < NB; ++i) tmem_ld16(tb + i * 16, reinterpret_cast<uint32_t(&)[16]>(v[i * 16]));
+    };
+    auto complete = [&](uint32_t u, uint32_t (&v)[W]) {
+#pragma unroll
+      for (int i = 0; i < NB; ++i) tmem_ld_wait_dep16(reinterpret_cast<uint32_t(&)[16]>(v[i * 16]));  // the first one waits
+      const uint32_t it = u / batches, bt = u - it * batches;
+      if (bt + 1 == batches) {  // accumulator fully read: hand the buffer back to the MMA issuer
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[it % p.tbufs]);
+      }
+    };
+    auto process = [&](uint32_t u, uint32_t (&v)[W]) {
+      const uint32_t it = u / batches, bt = u - it * batches;
+      const int64_t t = t_first + static_cast<int64_t>(it) * gridDim.x;
       const int64_t row = t * BLOCK_M + et;
       const bool row_ok = row < p.n;
       const float hn = (L2 && row_ok) ? p.half_norm[row] : 0.f;
-      mbar_wait(&tfull[b], bph);
-      tc_fence_after();
-      const uint32_t tbase = taddr + b * p.tbuf_stride;
-      // two register buffers: the tcgen05.ld of slice ch+1 is in flight while slice ch is filtered
-      uint32_t va[16], vb[16];
-      tmem_ld16(tbase, va);
-#pragma unroll 1
-      for (int ch = 0; ch < chunks; ch += 2) {
-        tmem_ld_wait_dep16(va);
-        const bool more = ch + 1 < chunks;
-        if (more) tmem_ld16(tbase + (ch + 1) * 16, vb);
-        else {  // accumulator fully read: hand the buffer back to the MMA issuer
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[b]);
-        }
-        k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
-        if (more) {
-          tmem_ld_wait_dep16(vb);
-          if (ch + 2 < chunks) tmem_ld16(tbase + (ch + 2) * 16, va);
-          else {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[b]);
-          }
-          k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
-        }
+#pragma unroll
+      for (int i = 0; i < NB; ++i) {
+        const int ch = static_cast<int>(bt) * NB + i;
+        if (ch < chunks) k2t_chunk<L2>(reinterpret_cast<uint32_t(&)[16]>(v[i * 16]), ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
       }
-      if (++since_check < check_every) continue;
+      if (bt + 1 != batches) return;
+      // ---- end of a tile ----
+      if (p.no_check || ++since_check < check_every) return;
       since_check = 0;
-      // ---- every check_every tiles: could any query's buffer overflow before the next check? ----
-      // A query gains <= 128 entries per tile, so <= 128*check_every between checks.  The count read here may miss appends of
-      // warps still inside this interval's last tile, hence a margin of TWO intervals; the barrier orders all appends
-      // before the exact re-read below.
+      // Every check_every tiles: could any query's buffer overflow before the next check?  A query gains <= 128 entries per
+      // tile, so <= 128*check_every between checks.  The count read here may miss appends of warps still inside this
+      // interval's last tile, hence a margin of TWO intervals; the barrier orders all appends before the exact re-read below.
       const bool any_full = epi_bar_or(et < p.nq && cnt_s[et] > full_mark);
       if (any_full) {
         for (int qi = ew; qi < p.nq; qi += 4) {  // warp w prunes queries w, w+4, ...
@@ -263,20 +284,39 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         if (tau_next > tau_s[et]) tau_s[et] = tau_next;
         tau_next = tau_load(p.sink.tau_g, et);
       }
+    };
+
+    uint32_t va[W], vb[W];
+    if (n_units > 0) issue(0, va);
+#pragma unroll 1
+    for (uint32_t u = 0; u < n_units; u += 2) {
+      complete(u, va);
+      if (u + 1 < n_units) issue(u + 1, vb);
+      process(u, va);
+      if (u + 1 < n_units) {
+        complete(u + 1, vb);
+        if (u + 2 < n_units) issue(u + 2, va);
+        process(u + 1, vb);
+      }
     }
 
-    // ---- end: prune every query to k and flush to the arena ----
+    // ---- end of the launch: the last one reduces every list to k' and flushes it to the arena; the others only record the
+    // list lengths (the lists stay where they are for the seed kernel and the next launch) ----
     epi_bar_sync();
-    for (int qi = ew; qi < p.nq; qi += 4) {
-      int n_q = cnt_s[qi];
-      Entry* buf = cta_cand + static_cast<int64_t>(qi) * cap;
-      if (n_q > k) {
-        const uint32_t kth = warp_prune(buf, n_q, k, my_hist);
-        if (lane == 0) atomicMax(&p.sink.tau_g[qi], kth);
-        n_q = k;
+    if (!p.last_pass) {
+      if (et < p.nq) p.cnt_g[static_cast<int64_t>(blockIdx.x) * p.nq_pad + et] = static_cast<uint32_t>(cnt_s[et]);
+    } else {
+      for (int qi = ew; qi < p.nq; qi += 4) {
+        int n_q = cnt_s[qi];
+        Entry* buf = cta_cand + static_cast<int64_t>(qi) * cap;
+        if (n_q > k) {
+          const uint32_t kth = warp_prune(buf, n_q, k, my_hist);
+          if (lane == 0) atomicMax(&p.sink.tau_g[qi], kth);
+          n_q = k;
+        }
+        __syncwarp();
+        warp_flush(p.sink, buf, n_q, qi);
       }
-      __syncwarp();
-      warp_flush(p.sink, buf, n_q, qi);
     }
   }
 
@@ -313,15 +353,22 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* co
   if (rc) return rc;
   const size_t smem = k2t_smem_bytes(p.kblocks, p.nq_pad, p.stages);
   const bool l2 = p.half_norm != nullptr;
-#define NXF_K2T_LAUNCH(B, L)                                                                                                          \
+#define NXF_K2T_LAUNCH_W(B, L, WW)                                                                                                    \
   do {                                                                                                                                \
-    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));     \
-    k2t_stream_kernel<B, L><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);                                                         \
+    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L, WW>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
+    k2t_stream_kernel<B, L, WW><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);                                                     \
+  } while (0)
+#define NXF_K2T_LAUNCH(B, L)                          \
+  do {                                                \
+    if (p.nq_pad <= 32) NXF_K2T_LAUNCH_W(B, L, 16);   \
+    else if (p.nq_pad <= 64) NXF_K2T_LAUNCH_W(B, L, 32); \
+    else NXF_K2T_LAUNCH_W(B, L, 64);                  \
   } while (0)
   if (bf16 && l2) NXF_K2T_LAUNCH(true, true);
   else if (bf16) NXF_K2T_LAUNCH(true, false);
   else if (l2) NXF_K2T_LAUNCH(false, true);
   else NXF_K2T_LAUNCH(false, false);
+#undef NXF_K2T_LAUNCH_W
 #undef NXF_K2T_LAUNCH
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;

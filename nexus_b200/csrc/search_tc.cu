@@ -361,6 +361,15 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           // published for the other owners of the query
           __syncwarp();  // this tile's appends (thread-private global stores) are visible to the warp
           unsigned need = __ballot_sync(kFullMask, cur.cnt > cap - BLOCK_N);
+          const bool prof = (p.debug & 32) && need;  // timing experiment: prune count / cycles per warp into the counter words
+          const long long pc0 = prof ? clock64() : 0;
+          const int pn = __popc(need);
+          if (need && !(p.debug & 64) && cur.cnt > cap - BLOCK_N) {
+            // the buffers were written tiles ago and may have left L2: every needy row pulls its own lines in now, so the serial
+            // warp-cooperative prunes below find them there
+            const char* b = reinterpret_cast<const char*>(warp_buf0 + static_cast<int64_t>(lane) * cap);
+            for (int o = 0; o < cur.cnt * 8; o += 128) prefetch_l2(b + o);
+          }
           while (need) {
             const int src = __ffs(need) - 1;
             need &= need - 1;
@@ -373,6 +382,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
             __syncwarp();
           }
+          if (prof && lane == 0) {
+            atomicAdd(reinterpret_cast<unsigned long long*>(p.prof), static_cast<unsigned long long>(pn));
+            atomicAdd(reinterpret_cast<unsigned long long*>(p.prof) + 1, static_cast<unsigned long long>(clock64() - pc0));
+          }
           if (valid) tau_next = tau_load(p.sink.tau_g, qrow);
         }
       }
@@ -380,6 +393,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
     // ---- end of the launch (pass): fold both slots' rows into the per-query global top-k' lists ----
     __syncwarp();
+    const long long mc0 = (p.debug & 32) ? clock64() : 0;
 #pragma unroll 1
     for (int slot = 0; slot < 2; ++slot) {
       if (qt_base + slot >= p.num_qt) break;
@@ -426,6 +440,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         __syncwarp();
       }
+    }
+    if ((p.debug & 32) && lane == 0) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof) + 2, static_cast<unsigned long long>(clock64() - mc0));
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof) + 3, 1ull);
     }
   }
 

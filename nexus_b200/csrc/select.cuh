@@ -1,7 +1,8 @@
 // select.cuh -- exact k-selection primitives shared by all search kernels.
 //
 //   warp_prune   : one warp reduces a candidate buffer in global memory (n > k entries) to its
-//                  exact top-k (unsorted, compacted to the front) and returns the k-th key.
+//                  exact top-k (unsorted, compacted to the front) and returns a threshold T with
+//                  exactly-k-or-ties semantics: T <= the k-th key, and every kept entry has key >= T.
 //                  Bitwise descent on the monotone 32-bit score key with warp REDUX counting (no shared
 //                  memory, no atomics), then one in-place compaction pass.
 //   Sink         : per-owner streaming top-k state (threshold tau, count, buffer) used by the
@@ -59,7 +60,10 @@ __device__ __noinline__ uint32_t warp_prune_reg(Entry* __restrict__ buf, int n, 
 #pragma unroll
       for (int r = 0; r < R; ++r) c += (key[r] >= cand) ? 1u : 0u;
       c = __reduce_add_sync(kFullMask, c);
-      if (c >= static_cast<unsigned>(k)) T = cand;
+      if (c >= static_cast<unsigned>(k)) {
+        T = cand;
+        if (c == static_cast<unsigned>(k)) break;  // exactly k keys >= cand: the top-k set is settled, cand is a lower bound of the k-th key
+      }
     }
   }
   const uint32_t kth = T;
@@ -116,7 +120,10 @@ __device__ __noinline__ uint32_t warp_prune_keys(Entry* __restrict__ buf, int n,
 #pragma unroll
       for (int r = 0; r < R; ++r) c += (key[r] >= cand) ? 1u : 0u;
       c = __reduce_add_sync(kFullMask, c);
-      if (c >= static_cast<unsigned>(k)) T = cand;
+      if (c >= static_cast<unsigned>(k)) {
+        T = cand;
+        if (c == static_cast<unsigned>(k)) break;  // exactly k keys >= cand: the top-k set is settled, cand is a lower bound of the k-th key
+      }
     }
   }
   const uint32_t kth = T;
@@ -182,9 +189,11 @@ static __device__ __noinline__ uint32_t warp_prune_mem(Entry* __restrict__ buf, 
       n2 = __reduce_add_sync(kFullMask, n2);
       n1 = __reduce_add_sync(kFullMask, n1);
       const unsigned kk = static_cast<unsigned>(k);
+      unsigned hit = n3;
       if (n3 >= kk) T = c3;
-      else if (n2 >= kk) T = c2;
-      else if (lo != 0u && n1 >= kk) T = c1;
+      else if (n2 >= kk) { T = c2; hit = n2; }
+      else if (lo != 0u && n1 >= kk) { T = c1; hit = n1; }
+      if (hit == kk) break;  // exactly k keys >= T
     }
   }
   const uint32_t kth = T;

@@ -84,9 +84,11 @@ def test_stream_kernel(case, nq, store):
     c, x = gen_inputs(n, d, nq, seed=200 + d)
     # 16-bit storage with more than one query goes to the tensor-core streaming kernel (K2T); K2 keeps nq = 1 and fp32 storage
     # ... and single queries on long rows (>= 512 B), where it already sits on the HBM roofline
+    # fp32 storage: K2 for one query, K2T over the bf16 [hi | mid] shadow from two
     long_rows = (d + 63) // 64 * 64 * 2 >= 512
-    run_and_check(c, x, k, store=store, path="auto", expect_path="stream" if (store == "f32" or (nq == 1 and long_rows)) else "tstream")
-    if store != "f32":
+    k2 = nq == 1 and (store == "f32" or long_rows)
+    run_and_check(c, x, k, store=store, path="auto", expect_path="stream" if k2 else "tstream")
+    if not k2:
         run_and_check(c, x, k, store=store, path="stream", expect_path="stream")
 
 
@@ -102,6 +104,36 @@ def test_tensor_stream_kernel(case, store):
     c, x = gen_inputs(n, d, q, seed=500 + n % 79)
     run_and_check(c, x, k, store=store, path="auto", rtol=1e-5, expect_path="tstream", min_recall=0.999)
     run_and_check(c, x, k, store=store, path="tstream_raw", rtol=2e-4, atol=2e-5, expect_path="tstream", min_recall=0.999)
+
+
+@pytest.mark.parametrize("case", [
+    # N, D, Q, k, expected default path
+    (3000, 64, 1, 10, "stream"), (3000, 64, 2, 10, "tstream"), (3000, 64, 16, 10, "tstream"), (5000, 128, 17, 100, "tstream"), (20000, 384, 33, 10, "tstream"),
+    (9000, 768, 32, 100, "tstream"), (9000, 768, 64, 100, "tensor"), (4096, 96, 100, 500, "tstream"), (2500, 100, 5, 7, "tstream"),
+    (40000, 64, 128, 500, "tstream"), (7001, 1536, 16, 10, "tstream"),
+])
+def test_tensor_stream_kernel_fp32_storage(case):
+    """K2T over the bf16 [hi | mid] shadow of fp32 rows: a c_hi block meets q_hi and q_mid, a c_mid block q_hi."""
+    n, d, q, k, expect = case
+    c, x = gen_inputs(n, d, q, seed=700 + n % 67)
+    run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, expect_path=expect)
+    if expect == "tstream":
+        run_and_check(c, x, k, store="f32", path="tstream_raw", rtol=2e-5, atol=4e-6, expect_path="tstream", min_recall=0.999)
+
+
+@pytest.mark.parametrize("store,case", [
+    ("bf16", (320000, 64, 128, 500)), ("bf16", (400000, 64, 7, 10)), ("f16", (310000, 128, 33, 100)), ("f32", (330000, 64, 40, 20)),
+    ("bf16", (350000, 64, 128, 1)), ("bf16", (1300000, 64, 40, 10)), ("bf16", (80000, 64, 128, 300)),
+])
+def test_tensor_stream_kernel_seeded(store, case):
+    """Longer corpora are searched in up to three launches (one tile per CTA, 16 more, the rest); between them the seed kernel raises
+    tau_g to the k'-th best over all per-CTA lists of the query: same results."""
+    n, d, q, k = case
+    c, x = gen_inputs(n, d, q, seed=800 + n % 61)
+    idx, D, I, rep, st = run_and_check(c, x, k, store=store, path="auto", rtol=1e-5, expect_path="tstream", min_recall=0.999)
+    kf = k + max(16, (k + 3) // 4)
+    if q * kf >= 768:                    # the library's policy: seed when nq * k' >= 768
+        assert st["kernel_launches"] >= 6    # 2 converts, seed pass, seed threshold, main pass, merge
 
 
 def test_tensor_stream_falls_back_when_queries_do_not_fit():
@@ -134,7 +166,7 @@ def test_tensor_kernel_fp32_storage(case):
     over-fetch and fp32 re-score.  Default dispatch above the stream kernel's batch; results to the fp32 tolerance."""
     n, d, q, k = case
     c, x = gen_inputs(n, d, q, seed=600 + n % 71)
-    run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, expect_path="tensor" if q > 4 else "stream")
+    run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, expect_path="tensor" if q > 128 else "tstream")
     run_and_check(c, x, k, store="f32", path="tensor", rtol=1e-5, expect_path="tensor")
     # without the re-score the scores are the three-product sums themselves: 2^-16 per term
     run_and_check(c, x, k, store="f32", path="tensor_raw", rtol=2e-5, atol=4e-6, expect_path="tensor", min_recall=0.999)
@@ -143,7 +175,7 @@ def test_tensor_kernel_fp32_storage(case):
 def test_tensor_fp32_storage_follows_adds_and_reset():
     """The shadow is built on first use and extended / rebuilt when rows are added, the storage grows or the index is reset."""
     from nexus_b200 import FlatIndex
-    c, x = gen_inputs(9000, 200, 64, seed=31)
+    c, x = gen_inputs(9000, 200, 200, seed=31)
     idx = FlatIndex(200, "ip", "f32")
     idx.add(c[:2000])
     for upto in (2000, 2500, 9000):
@@ -276,7 +308,5 @@ def test_errors_are_loud():
         idx.search(np.zeros((1, 16), np.float32), 0)
     with pytest.raises(ValueError):
         idx.search(np.zeros((1, 16), np.float32), 5000)
-    with pytest.raises(Exception):
-        idx.search(np.zeros((9, 16), np.float32), 2, flags=FLAGS["tstream"])  # f32 storage has no tensor stream kernel
     with pytest.raises(Exception):
         idx.search(np.zeros((9, 16), np.float32), 2, flags=FLAGS["tensor"] | FLAGS["exact"])   # two forced paths

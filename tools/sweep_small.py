@@ -20,11 +20,13 @@ def main():
     ap.add_argument("--k", type=int, default=0)
     ap.add_argument("--nqs", default="1,2,4,8,32,128")
     ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--store", default="", help="override the storage dtype (f32 | bf16 | f16)")
     a = ap.parse_args()
     import torch
     from nexus_b200 import FlatIndex
     Q, N, D, k, store, norm, desc = bench.CONFIGS[a.config]
     N, k = a.n or N, a.k or k
+    store = a.store or store
     dev = torch.device("cuda", 0)
     idx = FlatIndex(D, "ip", store, device=0)
     idx.reserve(N)
@@ -54,7 +56,7 @@ def main():
         kms = st["main_kernel_ms"] / max(1, st["main_kernel_count"])
         total = e0.elapsed_time(e1) / a.iters
         gbs = N * ld * esz / (kms * 1e-3) / 1e9
-        print(json.dumps({"config": a.config, "n": N, "dim": D, "k": k, "nq": nq, "path": st["last_path_name"], "kernel_ms": round(kms, 4),
+        print(json.dumps({"config": a.config, "n": N, "dim": D, "store": store, "k": k, "nq": nq, "path": st["last_path_name"], "kernel_ms": round(kms, 4),
                           "call_ms": round(total, 4), "GBps": round(gbs, 1), "frac_of_measured_hbm": round(gbs / peaks["hbm_gbs"], 3),
                           "qps": round(nq / (total * 1e-3), 1), "grid": st["last_grid"], "chunks": st["last_chunks"]}), flush=True)
 
