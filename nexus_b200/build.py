@@ -60,7 +60,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         o = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
         if not force and os.path.exists(o) and os.path.getmtime(o) >= max(os.path.getmtime(s), hdr_mtime):
             return src, 0, ""
-        cmd = [nvcc, *NVCC_FLAGS, "-I", INCLUDE, "-c", s, "-o", o]
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("NXF_EXTRA_NVCC_FLAGS", "").split(), "-I", INCLUDE, "-c", s, "-o", o]
         r = subprocess.run(cmd, capture_output=True, text=True)
         return src, r.returncode, r.stdout + r.stderr
 

@@ -81,31 +81,27 @@ __device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], int ch, floa
 #pragma unroll
   for (int j = 3; j < 15; j += 2) m = fmax3(m, d[j], d[j + 1]);
   m = fmaxf(m, d[15]);
-  const bool mine = m > 0.f && row_ok;
-  if (__any_sync(kFullMask, mine)) {  // warp-uniform: the whole (converged) epilogue warp takes the slow path together
+  if (m > 0.f && row_ok) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      const bool h = mine && d[j] > 0.f;  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
-      if (__any_sync(kFullMask, h)) {     // uniform: only the columns some row actually beats cost more than a vote
-        if (h) {
-          const int qi = ch * 16 + j;
-          const int pos = atomicAdd(&cnt_s[qi], 1);
-          const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
-          cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
-          cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
-        }
+      if (d[j] > 0.f) {  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
+        const int qi = ch * 16 + j;
+        const int pos = atomicAdd(&cnt_s[qi], 1);
+        const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
+        cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
+        cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
       }
     }
   }
 }
 
-// W = accumulator columns per tcgen05.ld batch (16, 32 or 64): a tile's nq_pad columns are one or two batches
-template <bool BF16, bool L2, int W>
+template <bool BF16, bool L2>
 __global__ void __launch_bounds__(k2t::THREADS, 1)
 k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K2TParams p) {
   using namespace k2t;
   extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment by pointer arithmetic on the shared array itself (an integer round trip would make every later access generic)
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int q_bytes = p.kblocks * p.nq_pad * 128;          // resident queries: [kblocks][nq_pad rows][128 B], 1024-aligned blocks
   unsigned char* q_smem = smem;
   unsigned char* ring = smem + ((q_bytes + 1023) & ~1023);
@@ -213,56 +209,49 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int chunks = p.nq_pad / 16;
     const int check_every = p.check_every;           // tiles between two overflow checks / threshold refreshes
     const int full_mark = cap - 2 * check_every * BLOCK_M;  // == 2k': see the margin note below
+    uint32_t iter = 0;
     int since_check = 0;
     float tau_next = (et < p.nq) ? tau_load(p.sink.tau_g, et) : INFINITY;
 
-    // The tile's accumulator is read in `batches` tcgen05.ld batches of W columns.  tcgen05.wait::ld waits for every outstanding
-    // load of the thread, so the software pipeline is two batches deep over the flat sequence of (tile, batch) units: while
-    // unit u is filtered, the load of unit u + 1 -- possibly the next tile's first batch -- is in flight.
-    constexpr int NB = W / 16;
-    const uint32_t batches = static_cast<uint32_t>((p.nq_pad + W - 1) / W);
-    const uint32_t n_it = t_first < t_end ? static_cast<uint32_t>((t_end - t_first + gridDim.x - 1) / gridDim.x) : 0u;
-    const uint32_t n_units = n_it * batches;
-
-    auto issue = [&](uint32_t u, uint32_t (&v)[W]) {
-      const uint32_t it = u / batches, bt = u - it * batches;
-      const uint32_t b = it % p.tbufs, bph = (it / p.tbufs) & 1;
-      if (bt == 0) {
-        mbar_wait(&tfull[b], bph);
-        tc_fence_after();
-      }
-      const uint32_t tb = taddr + b * p.tbuf_stride + bt * W;
-#pragma unroll
-      for (int i = 0; i < NB; ++i) tmem_ld16(tb + i * 16, reinterpret_cast<uint32_t(&)[16]>(v[i * 16]));
-    };
-    auto complete = [&](uint32_t u, uint32_t (&v)[W]) {
-#pragma unroll
-      for (int i = 0; i < NB; ++i) tmem_ld_wait_dep16(reinterpret_cast<uint32_t(&)[16]>(v[i * 16]));  // the first one waits
-      const uint32_t it = u / batches, bt = u - it * batches;
-      if (bt + 1 == batches) {  // accumulator fully read: hand the buffer back to the MMA issuer
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[it % p.tbufs]);
-      }
-    };
-    auto process = [&](uint32_t u, uint32_t (&v)[W]) {
-      const uint32_t it = u / batches, bt = u - it * batches;
-      const int64_t t = t_first + static_cast<int64_t>(it) * gridDim.x;
+    for (int64_t t = t_first; t < t_end; t += gridDim.x, ++iter) {
+      const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
       const int64_t row = t * BLOCK_M + et;
       const bool row_ok = row < p.n;
       const float hn = (L2 && row_ok) ? p.half_norm[row] : 0.f;
-#pragma unroll
-      for (int i = 0; i < NB; ++i) {
-        const int ch = static_cast<int>(bt) * NB + i;
-        if (ch < chunks) k2t_chunk<L2>(reinterpret_cast<uint32_t(&)[16]>(v[i * 16]), ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+      mbar_wait(&tfull[b], bph);
+      tc_fence_after();
+      const uint32_t tbase = taddr + b * p.tbuf_stride;
+      // two register buffers: the tcgen05.ld of slice ch+1 is in flight while slice ch is filtered
+      uint32_t va[16], vb[16];
+      tmem_ld16(tbase, va);
+#pragma unroll 1
+      for (int ch = 0; ch < chunks; ch += 2) {
+        tmem_ld_wait_dep16(va);
+        const bool more = ch + 1 < chunks;
+        if (more) tmem_ld16(tbase + (ch + 1) * 16, vb);
+        else {  // accumulator fully read: hand the buffer back to the MMA issuer
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[b]);
+        }
+        k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+        if (more) {
+          tmem_ld_wait_dep16(vb);
+          if (ch + 2 < chunks) tmem_ld16(tbase + (ch + 2) * 16, va);
+          else {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[b]);
+          }
+          k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+        }
       }
-      if (bt + 1 != batches) return;
-      // ---- end of a tile ----
-      if (p.no_check || ++since_check < check_every) return;
+      if (p.no_check || ++since_check < check_every) continue;
       since_check = 0;
-      // Every check_every tiles: could any query's buffer overflow before the next check?  A query gains <= 128 entries per
-      // tile, so <= 128*check_every between checks.  The count read here may miss appends of warps still inside this
-      // interval's last tile, hence a margin of TWO intervals; the barrier orders all appends before the exact re-read below.
+      // ---- every check_every tiles: could any query's buffer overflow before the next check? ----
+      // A query gains <= 128 entries per tile, so <= 128*check_every between checks.  The count read here may miss appends of
+      // warps still inside this interval's last tile, hence a margin of TWO intervals; the barrier orders all appends
+      // before the exact re-read below.
       const bool any_full = epi_bar_or(et < p.nq && cnt_s[et] > full_mark);
       if (any_full) {
         for (int qi = ew; qi < p.nq; qi += 4) {  // warp w prunes queries w, w+4, ...
@@ -283,20 +272,6 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       if (et < p.nq) {
         if (tau_next > tau_s[et]) tau_s[et] = tau_next;
         tau_next = tau_load(p.sink.tau_g, et);
-      }
-    };
-
-    uint32_t va[W], vb[W];
-    if (n_units > 0) issue(0, va);
-#pragma unroll 1
-    for (uint32_t u = 0; u < n_units; u += 2) {
-      complete(u, va);
-      if (u + 1 < n_units) issue(u + 1, vb);
-      process(u, va);
-      if (u + 1 < n_units) {
-        complete(u + 1, vb);
-        if (u + 2 < n_units) issue(u + 2, va);
-        process(u + 1, vb);
       }
     }
 
@@ -353,22 +328,15 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* co
   if (rc) return rc;
   const size_t smem = k2t_smem_bytes(p.kblocks, p.nq_pad, p.stages);
   const bool l2 = p.half_norm != nullptr;
-#define NXF_K2T_LAUNCH_W(B, L, WW)                                                                                                    \
+#define NXF_K2T_LAUNCH(B, L)                                                                                                          \
   do {                                                                                                                                \
-    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L, WW>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
-    k2t_stream_kernel<B, L, WW><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);                                                     \
-  } while (0)
-#define NXF_K2T_LAUNCH(B, L)                          \
-  do {                                                \
-    if (p.nq_pad <= 32) NXF_K2T_LAUNCH_W(B, L, 16);   \
-    else if (p.nq_pad <= 64) NXF_K2T_LAUNCH_W(B, L, 32); \
-    else NXF_K2T_LAUNCH_W(B, L, 64);                  \
+    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));     \
+    k2t_stream_kernel<B, L><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);                                                         \
   } while (0)
   if (bf16 && l2) NXF_K2T_LAUNCH(true, true);
   else if (bf16) NXF_K2T_LAUNCH(true, false);
   else if (l2) NXF_K2T_LAUNCH(false, true);
   else NXF_K2T_LAUNCH(false, false);
-#undef NXF_K2T_LAUNCH_W
 #undef NXF_K2T_LAUNCH
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
