@@ -1,6 +1,7 @@
 // api.cu -- the C ABI of libnexus_flat.so (see include/nexus_flat.h): index handle, add / convert /
 // shard upload, search dispatch (K2 stream | K1 tcgen05 | KX exact), merge, pool+normalise.
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdlib>
 #include <cstring>
@@ -184,6 +185,23 @@ void plan_units(int num_qt, int64_t n_tiles, int grid, int* chunks_out, int64_t*
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// K1's arena slice of a query: the list left by the sample passes (<= k' entries) + up to k' entries from every cluster that owns a
+// piece of the query's tile in the last pass (a tile's line segment is cut by pieces of num_qt / clusters of its length)
+int64_t k1_arena_stride(int64_t clusters, int64_t num_qt, int k_fetch) {
+  const int64_t owners_max = std::min<int64_t>(clusters, (clusters + num_qt - 1) / std::max<int64_t>(num_qt, 1) + 1);
+  return (owners_max + 1) * k_fetch;
+}
+
+// Rank m in a sample of `s_tiles` of `n_tiles` corpus tiles whose score is, except with probability < e^-30 per query, exceeded by
+// at least k rows of the whole corpus: the number of global top-k rows that fall into the sample is hypergeometric, bounded by
+// the Poisson(k * s / n) upper tail P(X >= m) <= exp(-(m ln(m / lambda) - m + lambda)).
+int sample_rank(int k, int64_t s_tiles, int64_t n_tiles) {
+  const double lambda = static_cast<double>(k) * static_cast<double>(s_tiles) / static_cast<double>(std::max<int64_t>(n_tiles, 1));
+  int m = static_cast<int>(lambda) + 1;
+  while (m < k && m * std::log(m / lambda) - m + lambda < 30.0) ++m;
+  return m;
+}
 
 int env_int(const char* name, int dflt) {
   const char* v = std::getenv(name);
@@ -612,7 +630,9 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     // pruned between tiles once fewer than 256 (one tile of appends) slots are left
     P.cap = std::max(2, env_int("NXF_K1_CAP_MULT", 2)) * P.k_fetch + 256;
     P.owners = static_cast<int64_t>(P.grid) * 128 * 2;  // two query-tile slots per CTA
-    P.arena_stride = P.k_fetch;  // K1 folds every owner's candidates into ONE list of k' per query (merged under a lock)
+    // arena slice of a query: the list left by the sample passes (<= k' entries) + up to k' entries from every cluster that owns
+    // a piece of the query tile in the last pass
+    P.arena_stride = k1_arena_stride(used, P.num_qt, P.k_fetch);
   }
   return NXF_OK;
 }
@@ -683,6 +703,16 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   if (idx->n == 0) { P.path = NXF_PATH_NONE; batch = nq; P.arena_stride = 1; P.owners = 0; P.cap = 1; P.k_fetch = 0; P.k_eff = 0; P.rescore = 0; }
   const bool multi_batch = batch < nq;
 
+  // K1: the last launch of a multi-batch search holds fewer query tiles, so more clusters share a tile: its slices are longer
+  int64_t rem_arena = 0, rem_stride = 0;
+  if (P.path == NXF_PATH_TENSOR && multi_batch && nq % batch != 0) {
+    const int64_t rem = nq % batch;
+    const int64_t nqt = ceil_div64(rem, 128 * P.cta_group);
+    const int64_t cl = std::max<int64_t>(1, std::min<int64_t>(P.grid / P.cta_group, nqt * P.n_tiles));
+    rem_stride = k1_arena_stride(cl, nqt, P.k_fetch);
+    rem_arena = rem * rem_stride;
+  }
+
   // ---- carve scratch (two passes: size, then pointers) ----
   const size_t qsz = dtype_size(q_dtype);
   unsigned char* base = nullptr;
@@ -698,7 +728,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     tau_g = cv.take<uint32_t>(static_cast<size_t>(3 * nq_pad + 64));  // tau | qcnt | lock | K1 round counter
     qcnt = tau_g ? tau_g + nq_pad : nullptr;
     qlock = tau_g ? tau_g + 2 * nq_pad : nullptr;
-    arena = cv.take<Entry>(static_cast<size_t>(batch) * P.arena_stride);
+    arena = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(batch * P.arena_stride, rem_arena)));
     cand = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(P.owners, 1)) * P.cap);
     k2t_cnt = P.path == NXF_PATH_TSTREAM ? cv.take<uint32_t>(static_cast<size_t>(std::max<int64_t>(P.owners, 1))) : nullptr;
     if (!out_on_device) {
@@ -741,9 +771,10 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       NXF_CUDA(cudaEventCreate(&pe1));
       NXF_CUDA(cudaEventRecord(pe0, stream));
     }
+    const int64_t arena_stride = (P.path == NXF_PATH_TENSOR && bn < batch && rem_stride > 0) ? rem_stride : P.arena_stride;
     SinkParams sink;
     sink.tau_g = tau_g; sink.qcnt = qcnt; sink.lock = qlock; sink.arena = arena; sink.cand = cand;
-    sink.arena_stride = P.arena_stride; sink.cap = P.cap; sink.k = P.k_fetch;
+    sink.arena_stride = arena_stride; sink.cap = P.cap; sink.k = P.k_fetch;
 
     if (P.path == NXF_PATH_STREAM) {
       // K2 handles up to nq_t queries per launch; a forced stream search of more queries loops
@@ -831,30 +862,50 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       }
       NXF_REQUIRE(kp.num_qt <= grid / P.cta_group || P.n_tiles == 0, "nxf_search: internal: %d query tiles for %d clusters", kp.num_qt,
                   grid / P.cta_group);
-      // Seeded passes (DESIGN.md "threshold seeding"): a short prefix of the corpus first; its end-of-pass merge leaves every
-      // query's exact k'-th best of that prefix in tau_g, so the next, 32x longer pass starts with a threshold that already
-      // rejects all but ~32 k' scores per query, and the rest of the corpus one that rejects all but ~(N/prefix) k'.
+      // Sampled thresholds: two short passes over an evenly spread sample of the corpus tiles (1/256, then 1/16 of
+      // them) leave in tau_g the score of a rank chosen so that -- except with probability ~e^-30 per query -- at least k' rows of
+      // the whole corpus beat it; the main pass over the other tiles then keeps ~3 k' candidates per query instead of
+      // k' ln(N / k') per owner.  The counts are verified afterwards; a query that came back short is searched again.
       int64_t bounds[4] = {0, 0, 0, P.n_tiles};
       int n_pass = 0;
+      kp.perm_s = kp.perm_ns = kp.perm_s0 = kp.perm_n0 = 0;
+      kp.run_flag = nullptr;
       {
-        const int64_t a = std::min<int64_t>(P.n_tiles, P.round_tiles), b = std::min<int64_t>(P.n_tiles, 32 * a);
-        int64_t cuts[2] = {a, b};
-        int64_t prev = 0;
-        // measured on C2: the seed passes pay for themselves only when k' is large (NXF_K1_SEED=0/1 overrides)
-        const int seed_env = env_int("NXF_K1_SEED", -1);
-        const bool seed = seed_env >= 0 ? seed_env != 0 : P.k_fetch >= 512;
-        for (int c = 0; c < 2; ++c)
-          if (seed && kp.num_qt > 1 && cuts[c] > prev && 4 * cuts[c] <= P.n_tiles) { bounds[++n_pass] = cuts[c]; prev = cuts[c]; }
+        const int est_env = env_int("NXF_K1_EST", -1);
+        const int64_t s1 = std::max(2, env_int("NXF_K1_EST_S1", 16)), s0 = std::max(2, env_int("NXF_K1_EST_S0", 16));
+        const bool est = (est_env >= 0 ? est_env != 0 : true) && P.n_tiles >= 4 * s1 * s0 && kp.debug == 0;
+        if (est) {
+          kp.perm_s = s1; kp.perm_ns = ceil_div64(P.n_tiles, s1);
+          kp.perm_s0 = s0; kp.perm_n0 = ceil_div64(kp.perm_ns, s0);
+          bounds[++n_pass] = kp.perm_n0;
+          bounds[++n_pass] = kp.perm_ns;
+        }
         bounds[++n_pass] = P.n_tiles;
       }
       for (int ps = 0; ps < n_pass; ++ps) {
+        const bool last = ps + 1 == n_pass;
         kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
+        kp.sink.k = last ? P.k_fetch : std::min(P.k_fetch, sample_rank(P.k_fetch, bounds[ps + 1], P.n_tiles));
+        kp.final_flush = last ? 1 : 0;
         kp.sync_ctr = tau_g + 3 * nq_pad + ps;   // one round counter per pass (all zeroed above)
         kp.prof = tau_g + 3 * nq_pad + 16;
         rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
                      : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
         if (rc) return rc;
         idx->stats.kernel_launches++;
+      }
+      if (n_pass > 1) {
+        // verification + fall-back: the launch below returns at once unless some query holds fewer than min(k', n) candidates
+        uint32_t* flag = tau_g + 3 * nq_pad + 8;
+        rc = launch_verify_counts(qcnt, tau_g, bn, static_cast<int>(std::min<int64_t>(P.k_fetch, idx->n)), flag, stream);
+        if (rc) return rc;
+        kp.tile_begin = 0; kp.tile_end = P.n_tiles; kp.sink.k = P.k_fetch; kp.final_flush = 1;
+        kp.run_flag = flag;
+        kp.sync_ctr = tau_g + 3 * nq_pad + 3;
+        rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
+                     : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
+        if (rc) return rc;
+        idx->stats.kernel_launches += 2;
       }
     }
 
@@ -870,7 +921,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       idx->prof_events.emplace_back(pe0, pe1);
     }
     MergeArenaParams mp;
-    mp.arena = arena; mp.qcnt = qcnt; mp.arena_stride = P.arena_stride; mp.k_fetch = P.k_fetch; mp.k_out = k; mp.metric = idx->metric;
+    mp.arena = arena; mp.qcnt = qcnt; mp.arena_stride = arena_stride; mp.k_fetch = P.k_fetch; mp.k_out = k; mp.metric = idx->metric;
     mp.rescore = P.rescore; mp.q = q_f32; mp.ldq = idx->ld; mp.corpus = idx->data; mp.ld = idx->ld; mp.dim = idx->dim;
     mp.id_offset = idx->id_offset;
     mp.out_scores = out_on_device ? out_scores + b0 * k : o_scores;

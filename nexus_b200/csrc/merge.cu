@@ -331,6 +331,31 @@ int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, in
   return NXF_OK;
 }
 
+// ---- verification of sampled thresholds --------------------------------------------------------
+// K1 starts its main pass from a threshold ESTIMATED on a sample (DESIGN.md "sampled thresholds"); the estimate is below the
+// true k'-th score except with probability ~e^-30 per query.  A query for which fewer than `need` candidates came back is
+// searched again from scratch by the fall-back pass: its slice is emptied and its threshold reset, every other query gets
+// +inf (the fall-back pass then appends nothing for it), and *flag tells the fall-back launch whether to run at all.
+__global__ void __launch_bounds__(256) verify_counts_kernel(uint32_t* __restrict__ qcnt, uint32_t* __restrict__ tau_g, int64_t nq, int need,
+                                                            uint32_t* flag) {
+  const int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (q >= nq) return;
+  if (qcnt[q] < static_cast<uint32_t>(need)) {
+    qcnt[q] = 0u;
+    tau_g[q] = 0u;
+    atomicOr(flag, 1u);
+  } else {
+    tau_g[q] = 0xFF800000u;  // okey(+inf)
+  }
+}
+
+int launch_verify_counts(uint32_t* qcnt, uint32_t* tau_g, int64_t nq, int need, uint32_t* flag, cudaStream_t stream) {
+  if (nq <= 0) return NXF_OK;
+  verify_counts_kernel<<<static_cast<unsigned>((nq + 255) / 256), 256, 0, stream>>>(qcnt, tau_g, nq, need, flag);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
 // ---- multi-list merge (multi-GPU shard merge) ---------------------------------------------------
 __global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(MergeListsParams p) {
   __shared__ uint64_t keys[mg::MAXK];

@@ -29,7 +29,13 @@ struct K1Params {
   int split_kb; // 0, or (fp32 storage as two bf16 planes [hi | mid] per row, each split_kb blocks wide) the plane width: the three
                 // segments of a tile are (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
   int num_qt;   // query tiles of 128*CG rows (<= number of clusters)
-  int64_t tile_begin, tile_end;  // corpus tiles [begin, end) of this pass (a search is 1-3 passes: seed, seed, rest)
+  int64_t tile_begin, tile_end;  // (virtual) corpus tiles [begin, end) of this pass (a search is 1-3 passes: sample, sample, rest)
+  // virtual -> physical tile order (DESIGN.md "sampled thresholds"): the first perm_ns virtual tiles are the physical tiles
+  // 0, s, 2s, ... (of those, every s0-th comes first: perm_n0 tiles), then all the others in order.  perm_s <= 1: identity
+  int64_t perm_s, perm_ns, perm_s0, perm_n0;
+  const uint32_t* run_flag;  // not NULL: the launch does nothing unless *run_flag != 0 (the fall-back pass after a failed verification)
+  int final_flush;     // end of the pass: 1 = rows (reduced to k' if longer) are appended to the query's arena slice, 0 = they are
+                       // merged into the query's list of sink.k entries under the lock, whose sink.k-th best goes to tau_g
   int round_tiles;     // corpus tiles per round (the L2-resident window)
   int sync_window;     // soft round barrier: a producer may run this many rounds ahead of the rest (0 = no barrier)
   uint32_t* sync_ctr;  // [1] zeroed per launch: rounds completed, summed over clusters
@@ -117,6 +123,7 @@ size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages);
 int k2t_plan_stages(int kblocks, int nq_pad);
 int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g, int nq,
                           cudaStream_t stream);
+int launch_verify_counts(uint32_t* qcnt, uint32_t* tau_g, int64_t nq, int need, uint32_t* flag, cudaStream_t stream);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,

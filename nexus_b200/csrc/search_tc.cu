@@ -140,6 +140,21 @@ __device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0,
   return rp;
 }
 
+// virtual -> physical corpus tile (K1Params::perm_*): sample tiles first, spread evenly over the corpus
+__device__ __forceinline__ int64_t phys_tile(const K1Params& p, int64_t v) {
+  if (p.perm_s <= 1) return v;
+  if (v >= p.perm_ns) {  // the j-th tile that is not a multiple of s
+    const int64_t j = v - p.perm_ns;
+    return j + j / (p.perm_s - 1) + 1;
+  }
+  int64_t i = v;  // index among the multiples of s
+  if (p.perm_s0 > 1) {
+    if (v < p.perm_n0) i = v * p.perm_s0;
+    else { const int64_t j = v - p.perm_n0; i = j + j / (p.perm_s0 - 1) + 1; }
+  }
+  return i * p.perm_s;
+}
+
 template <int CG, bool BF16>
 __global__ void __launch_bounds__(k1::THREADS, 1)
 k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K1Params p) {
@@ -155,6 +170,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint32_t* tmem_ptr_s = reinterpret_cast<uint32_t*>(tempty + 2);
   uint32_t* hist = tmem_ptr_s + 4;
 
+  if (p.run_flag != nullptr && ld_relaxed_u32(p.run_flag) == 0u) return;  // uniform over the grid: written by an earlier kernel
   const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
   const unsigned lane = lane_id();
   const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
@@ -199,7 +215,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           const int64_t lo = pos - qt * rp.R, hi = min(rp.b - qt * rp.R, rp.R);
           const int32_t q_row0 = static_cast<int32_t>((qt * CG + rank) * BLOCK_M);
           for (int64_t t = r0 + lo; t < r0 + hi; ++t) {
-            const int32_t c_row0 = static_cast<int32_t>(t * BLOCK_N + rank * C::LOAD_N);
+            const int32_t c_row0 = static_cast<int32_t>(phys_tile(p, t) * BLOCK_N + rank * C::LOAD_N);
             for (int kb = 0; kb < p.kblocks; ++kb) {
               // column (in elements) of this K block in the query / corpus rows; split storage walks (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
               int32_t q_col = kb * BLOCK_K, c_col = kb * BLOCK_K;
@@ -317,7 +333,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
           mbar_wait(&tfull[as], aph);
           tc_fence_after();
-          const int32_t col0 = static_cast<int32_t>(t * BLOCK_N);
+          const int32_t col0 = static_cast<int32_t>(phys_tile(p, t) * BLOCK_N);
           // slow-path epilogue: the last corpus tile (rows past n are TMA zero fill) or the L2 metric
           const bool adj = (col0 + BLOCK_N > n_rows) || (p.half_norm != nullptr);
           const uint32_t tbase = taddr + as * BLOCK_N;
@@ -408,6 +424,11 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         int n = __shfl_sync(kFullMask, my_cnt, src);
         if (n == 0) continue;  // uniform
         Entry* buf = warp_buf0 + static_cast<int64_t>(src) * cap;
+        if (p.final_flush) {  // last pass: no merge, the row's candidates (its k' best if it holds more) go to the arena slice
+          if (n > k) { warp_prune(buf, n, k, my_hist); n = k; __syncwarp(); }
+          warp_flush(p.sink, buf, n, q);
+          continue;
+        }
         // per-query lock: the list is read-modify-written once by each of the (<= 4) owners of the query
         if (lane == 0) {
           while (atomicCAS(&p.sink.lock[q], 0u, 1u) != 0u) __nanosleep(100);

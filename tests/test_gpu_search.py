@@ -199,6 +199,34 @@ def test_tensor_fp32_storage_l2():
     run_and_check(c, x, 50, store="f32", path="auto", metric="l2", rtol=2e-4, atol=1e-3, expect_path="tensor", min_recall=0.999)
 
 
+@pytest.mark.parametrize("store,case", [
+    ("bf16", (300000, 64, 300, 100)), ("bf16", (270000, 128, 700, 10)), ("f16", (300000, 64, 260, 1000)), ("f32", (280000, 64, 150, 50)),
+    ("bf16", (262144 + 77, 64, 129, 300)),
+])
+def test_tensor_kernel_sampled_thresholds(store, case):
+    """Corpora of >= 1024 tiles: K1 runs two sample passes (1/256 and 1/16 of the tiles, spread evenly), starts the main pass from
+    the sampled-rank threshold, verifies the candidate counts and falls back for queries that came back short: same results."""
+    n, d, q, k = case
+    c, x = gen_inputs(n, d, q, seed=900 + n % 59)
+    idx, D, I, rep, st = run_and_check(c, x, k, store=store, path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
+    assert st["kernel_launches"] >= 8    # 2 converts, 3 passes, verification, fall-back launch, merge
+
+
+def test_tensor_kernel_sampled_thresholds_fallback():
+    """An adversarial corpus: every row that matters lies in a SAMPLE tile (physical tiles 0, 16, 32, ...), so the sampled threshold is
+    far too high, the main pass finds nothing and the verification must send every query through the fall-back pass."""
+    n, d, q, k = 300000, 64, 200, 100
+    rng = np.random.default_rng(5)
+    c = (0.05 * rng.standard_normal((n, d))).astype(np.float32)
+    x = rng.standard_normal((q, d)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    tile = np.arange(n) // 256
+    hot = np.flatnonzero(tile % 16 == 0)
+    c[hot] += x[rng.integers(0, q, size=hot.size)] * rng.uniform(0.5, 1.0, size=(hot.size, 1)).astype(np.float32)
+    run_and_check(c, x, k, store="bf16", path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
+    run_and_check(c, x, k, store="f32", path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
+
+
 def test_tensor_default_dispatch_and_bf16_recall_vs_fp32():
     """BASELINE bar: bf16 recall@k >= 0.999 against the fp32 reference on the same (bf16-valued) corpus."""
     c, x = gen_inputs(50000, 768, 512, seed=77)
