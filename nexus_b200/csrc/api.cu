@@ -866,10 +866,12 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       // them) leave in tau_g the score of a rank chosen so that -- except with probability ~e^-30 per query -- at least k' rows of
       // the whole corpus beat it; the main pass over the other tiles then keeps ~3 k' candidates per query instead of
       // k' ln(N / k') per owner.  The counts are verified afterwards; a query that came back short is searched again.
-      int64_t bounds[4] = {0, 0, 0, P.n_tiles};
-      int n_pass = 0;
       kp.perm_s = kp.perm_ns = kp.perm_s0 = kp.perm_n0 = 0;
       kp.run_flag = nullptr;
+      kp.prof = tau_g + 3 * nq_pad + 16;
+      struct Pass { int64_t begin, end; int k; int est_only; };
+      Pass passes[4];
+      int n_pass = 0;
       {
         const int est_env = env_int("NXF_K1_EST", -1);
         const int64_t s1 = std::max(2, env_int("NXF_K1_EST_S1", 16)), s0 = std::max(2, env_int("NXF_K1_EST_S0", 16));
@@ -877,31 +879,43 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
         if (est) {
           kp.perm_s = s1; kp.perm_ns = ceil_div64(P.n_tiles, s1);
           kp.perm_s0 = s0; kp.perm_n0 = ceil_div64(kp.perm_ns, s0);
-          bounds[++n_pass] = kp.perm_n0;
-          bounds[++n_pass] = kp.perm_ns;
+          // estimate-only pass: a few tiles per cluster (so that no row fills its buffer), only slice maxima are recorded; it spares
+          // the first sample pass the cost of starting from -inf (every score appended, every row pruned after its first tile)
+          const int64_t clusters = grid / P.cta_group;
+          const int64_t n_e = std::max<int64_t>(2, std::min<int64_t>(std::min<int64_t>(16, kp.perm_n0), 7 * clusters / std::max(kp.num_qt, 1)));
+          passes[n_pass++] = {0, n_e, std::min(P.k_fetch, sample_rank(P.k_fetch, n_e, P.n_tiles)), 1};
+          passes[n_pass++] = {0, kp.perm_n0, std::min(P.k_fetch, sample_rank(P.k_fetch, kp.perm_n0, P.n_tiles)), 0};
+          passes[n_pass++] = {kp.perm_n0, kp.perm_ns, std::min(P.k_fetch, sample_rank(P.k_fetch, kp.perm_ns, P.n_tiles)), 0};
+          passes[n_pass++] = {kp.perm_ns, P.n_tiles, P.k_fetch, 0};
+        } else {
+          passes[n_pass++] = {0, P.n_tiles, P.k_fetch, 0};
         }
-        bounds[++n_pass] = P.n_tiles;
       }
+      const int user_debug = kp.debug;
       for (int ps = 0; ps < n_pass; ++ps) {
-        const bool last = ps + 1 == n_pass;
-        kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
-        kp.sink.k = last ? P.k_fetch : std::min(P.k_fetch, sample_rank(P.k_fetch, bounds[ps + 1], P.n_tiles));
-        kp.final_flush = last ? 1 : 0;
+        kp.tile_begin = passes[ps].begin; kp.tile_end = passes[ps].end;
+        kp.sink.k = passes[ps].k;
+        kp.debug = user_debug | (passes[ps].est_only ? 128 : 0);
         kp.sync_ctr = tau_g + 3 * nq_pad + ps;   // one round counter per pass (all zeroed above)
-        kp.prof = tau_g + 3 * nq_pad + 16;
         rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
                      : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
         if (rc) return rc;
         idx->stats.kernel_launches++;
+        if (ps + 1 < n_pass) {
+          rc = launch_select_tau(arena, qcnt, arena_stride, passes[ps].k, tau_g, bn, passes[ps].est_only, stream);
+          if (rc) return rc;
+          idx->stats.kernel_launches++;
+        }
       }
+      kp.debug = user_debug;
       if (n_pass > 1) {
         // verification + fall-back: the launch below returns at once unless some query holds fewer than min(k', n) candidates
         uint32_t* flag = tau_g + 3 * nq_pad + 8;
         rc = launch_verify_counts(qcnt, tau_g, bn, static_cast<int>(std::min<int64_t>(P.k_fetch, idx->n)), flag, stream);
         if (rc) return rc;
-        kp.tile_begin = 0; kp.tile_end = P.n_tiles; kp.sink.k = P.k_fetch; kp.final_flush = 1;
+        kp.tile_begin = 0; kp.tile_end = P.n_tiles; kp.sink.k = P.k_fetch;
         kp.run_flag = flag;
-        kp.sync_ctr = tau_g + 3 * nq_pad + 3;
+        kp.sync_ctr = tau_g + 3 * nq_pad + 5;
         rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
                      : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
         if (rc) return rc;

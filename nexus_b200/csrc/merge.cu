@@ -331,6 +331,31 @@ int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, in
   return NXF_OK;
 }
 
+// ---- between two K1 passes: the slice's m-th best becomes the query's threshold ------------------
+// One warp per query: the slice (what the passes so far appended) is reduced in place to its m best entries, whose m-th score
+// goes to tau_g.  `reset` empties the slice instead (the estimate-only pass: its tiles are streamed again).
+__global__ void __launch_bounds__(256) select_tau_kernel(Entry* __restrict__ arena, uint32_t* __restrict__ qcnt, int64_t arena_stride, int m,
+                                                         uint32_t* tau_g, int64_t nq, int reset) {
+  const int64_t q = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
+  if (q >= nq) return;  // whole warps
+  const unsigned lane = threadIdx.x & 31;
+  int n = static_cast<int>(min(static_cast<int64_t>(qcnt[q]), arena_stride));
+  __syncwarp();
+  if (n > m) {
+    const uint32_t kth = warp_prune(arena + q * arena_stride, n, m, nullptr);
+    if (lane == 0) atomicMax(&tau_g[q], kth);
+    n = m;
+  }
+  if (lane == 0) qcnt[q] = reset ? 0u : static_cast<uint32_t>(n);
+}
+
+int launch_select_tau(Entry* arena, uint32_t* qcnt, int64_t arena_stride, int m, uint32_t* tau_g, int64_t nq, int reset, cudaStream_t stream) {
+  if (nq <= 0) return NXF_OK;
+  select_tau_kernel<<<static_cast<unsigned>((nq * 32 + 255) / 256), 256, 0, stream>>>(arena, qcnt, arena_stride, m, tau_g, nq, reset);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
 // ---- verification of sampled thresholds --------------------------------------------------------
 // K1 starts its main pass from a threshold ESTIMATED on a sample (DESIGN.md "sampled thresholds"); the estimate is below the
 // true k'-th score except with probability ~e^-30 per query.  A query for which fewer than `need` candidates came back is

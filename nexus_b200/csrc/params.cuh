@@ -34,8 +34,7 @@ struct K1Params {
   // 0, s, 2s, ... (of those, every s0-th comes first: perm_n0 tiles), then all the others in order.  perm_s <= 1: identity
   int64_t perm_s, perm_ns, perm_s0, perm_n0;
   const uint32_t* run_flag;  // not NULL: the launch does nothing unless *run_flag != 0 (the fall-back pass after a failed verification)
-  int final_flush;     // end of the pass: 1 = rows (reduced to k' if longer) are appended to the query's arena slice, 0 = they are
-                       // merged into the query's list of sink.k entries under the lock, whose sink.k-th best goes to tau_g
+  // end of every pass: each row's candidates (its sink.k best if it holds more) are appended to the query's arena slice
   int round_tiles;     // corpus tiles per round (the L2-resident window)
   int sync_window;     // soft round barrier: a producer may run this many rounds ahead of the rest (0 = no barrier)
   uint32_t* sync_ctr;  // [1] zeroed per launch: rounds completed, summed over clusters
@@ -123,6 +122,7 @@ size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages);
 int k2t_plan_stages(int kblocks, int nq_pad);
 int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g, int nq,
                           cudaStream_t stream);
+int launch_select_tau(Entry* arena, uint32_t* qcnt, int64_t arena_stride, int m, uint32_t* tau_g, int64_t nq, int reset, cudaStream_t stream);
 int launch_verify_counts(uint32_t* qcnt, uint32_t* tau_g, int64_t nq, int need, uint32_t* flag, cudaStream_t stream);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);

@@ -109,6 +109,13 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbas
     // entry index in the candidate arena (uniform base + 32-bit index: one IMAD.WIDE per address); score and row go out
     // as two 32-bit stores so that no register pairing is forced on the accumulator values of the common path
     uint32_t w = my_first + static_cast<uint32_t>(st.cnt);
+    if (debug & 128) {
+      // estimate-only pass: the slice maximum stands for the slice (its rank statistics bound the scores' from below)
+      cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(m);
+      cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(cbase);
+      st.cnt += 1;
+      return;
+    }
 #pragma unroll
     for (int q4 = 0; q4 < 4; ++q4) {
       if (g[q4] > tau) {
@@ -408,59 +415,39 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
     }
 
-    // ---- end of the launch (pass): fold both slots' rows into the per-query global top-k' lists ----
+    // ---- end of the launch (pass): every row's candidates (its sink.k best if it holds more) go to the query's arena slice ----
     __syncwarp();
     const long long mc0 = (p.debug & 32) ? clock64() : 0;
 #pragma unroll 1
     for (int slot = 0; slot < 2; ++slot) {
       if (qt_base + slot >= p.num_qt) break;
-      const int my_cnt = (slot == cur_slot) ? cur.cnt : alt.cnt;
+      int my_cnt = (slot == cur_slot) ? cur.cnt : alt.cnt;
       Entry* warp_buf0 = slot_buf0(slot);
-      const int64_t qrow0 = slot_qrow0(slot);
-#pragma unroll 1
-      for (int src = 0; src < 32; ++src) {
-        const int64_t q = qrow0 + src;
-        if (q >= p.nq) break;  // uniform
-        int n = __shfl_sync(kFullMask, my_cnt, src);
-        if (n == 0) continue;  // uniform
-        Entry* buf = warp_buf0 + static_cast<int64_t>(src) * cap;
-        if (p.final_flush) {  // last pass: no merge, the row's candidates (its k' best if it holds more) go to the arena slice
-          if (n > k) { warp_prune(buf, n, k, my_hist); n = k; __syncwarp(); }
-          warp_flush(p.sink, buf, n, q);
-          continue;
-        }
-        // per-query lock: the list is read-modify-written once by each of the (<= 4) owners of the query
-        if (lane == 0) {
-          while (atomicCAS(&p.sink.lock[q], 0u, 1u) != 0u) __nanosleep(100);
-          __threadfence();
-        }
+      const int64_t my_q = slot_qrow0(slot) + lane;
+      if (my_q >= p.nq) my_cnt = 0;
+      // rows holding more than sink.k entries are reduced first (rare once the thresholds are sampled)
+      unsigned big = __ballot_sync(kFullMask, my_cnt > k);
+      while (big) {
+        const int src = __ffs(big) - 1;
+        big &= big - 1;
+        const int n_src = __shfl_sync(kFullMask, my_cnt, src);
+        warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
+        if (static_cast<int>(lane) == src) my_cnt = k;
         __syncwarp();
-        const int m = static_cast<int>(ld_cg_u32(&p.sink.qcnt[q]));
-        if (n + m > cap) {  // own candidates do not leave room for the list: reduce them to k first
-          warp_prune(buf, n, k, my_hist);
-          n = k;
-          __syncwarp();
-        }
-        Entry* gl = p.sink.arena + q * p.sink.arena_stride;
-        for (int i = lane; i < m; i += 32) buf[n + i] = ld_cg_entry(gl + i);
-        __syncwarp();
-        int tot = n + m;
-        uint32_t kth = 0;
-        if (tot > k) {
-          kth = warp_prune(buf, tot, k, my_hist);
-          tot = k;
-          __syncwarp();
-        }
-        for (int i = lane; i < tot; i += 32) gl[i] = buf[i];
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) {
-          *reinterpret_cast<volatile uint32_t*>(&p.sink.qcnt[q]) = static_cast<uint32_t>(tot);
-          if (kth) atomicMax(&p.sink.tau_g[q], kth);  // exact k'-th best of everything folded so far: seeds the next pass
-          __threadfence();
-          atomicExch(&p.sink.lock[q], 0u);
-        }
-        __syncwarp();
+      }
+      // one atomic per row, all 32 in flight together; then the warp copies the rows one after the other
+      uint32_t my_pos = 0;
+      if (my_cnt > 0) my_pos = atomicAdd(&p.sink.qcnt[my_q], static_cast<uint32_t>(my_cnt));
+      if (static_cast<int64_t>(my_pos) + my_cnt > p.sink.arena_stride) my_cnt = 0;  // cannot happen by construction; never write OOB
+      unsigned todo = __ballot_sync(kFullMask, my_cnt > 0);
+      while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int n = __shfl_sync(kFullMask, my_cnt, src);
+        const uint32_t pos = __shfl_sync(kFullMask, my_pos, src);
+        const Entry* buf = warp_buf0 + static_cast<int64_t>(src) * cap;
+        Entry* dst = p.sink.arena + (slot_qrow0(slot) + src) * p.sink.arena_stride + pos;
+        for (int i = lane; i < n; i += 32) dst[i] = buf[i];
       }
     }
     if ((p.debug & 32) && lane == 0) {
