@@ -805,33 +805,51 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       const void* c_rows = P.split ? idx->split : idx->data;
       const int64_t c_ld = P.split ? 2 * idx->ld : idx->ld;
       const int c_dt = P.split ? NXF_BF16 : idx->store_dtype;
-      // Threshold seeding: up to two short launches first (one tile per CTA, then 16 more), each followed by the seed kernel, which
-      // raises tau_g to the k'-th best over ALL lists of the query; the last launch streams the rest with that threshold.
+      // Sampled thresholds, as in K1: up to two short launches over evenly spread sample tiles first (about one tile
+      // per CTA, then about 16 more); after each, the seed kernel raises tau_g to the sample's m-th best over ALL lists of the
+      // query (m from sample_rank(): at least k' rows of the corpus beat it except with probability ~e^-30).  The counts are
+      // verified after the last launch; a query that came back short is searched again from -inf by the fall-back launch.
+      kp.perm = TilePerm();
+      kp.run_flag = nullptr;
+      kp.cnt_g = k2t_cnt;
       int64_t bounds[4] = {0, 0, 0, P.n_tiles};
       int n_pass = 0;
       if (P.seed) {
         const int64_t g = P.grid;
-        int64_t prev = 0;
-        const int64_t cuts[2] = {g, 17 * g};
-        for (int c = 0; c < 2; ++c) {
-          // a cut is worth a launch when it leaves at least 4x as much behind it, and its sample holds well over k' rows
-          if (4 * cuts[c] <= P.n_tiles && cuts[c] * 128 >= 8 * static_cast<int64_t>(P.k_fetch)) { bounds[++n_pass] = cuts[c]; prev = cuts[c]; }
+        if (P.n_tiles >= 68 * g) {
+          kp.perm.s = P.n_tiles / (17 * g); kp.perm.ns = ceil_div64(P.n_tiles, kp.perm.s);
+          kp.perm.s0 = ceil_div64(kp.perm.ns, g); kp.perm.n0 = ceil_div64(kp.perm.ns, kp.perm.s0);
+          bounds[++n_pass] = kp.perm.n0;
+          bounds[++n_pass] = kp.perm.ns;
+        } else if (P.n_tiles >= 4 * g) {
+          kp.perm.s = P.n_tiles / g; kp.perm.ns = ceil_div64(P.n_tiles, kp.perm.s);
+          kp.perm.s0 = 1; kp.perm.n0 = kp.perm.ns;
+          bounds[++n_pass] = kp.perm.ns;
         }
-        (void)prev;
       }
       bounds[++n_pass] = P.n_tiles;
-      kp.cnt_g = k2t_cnt;
       for (int ps = 0; ps + 1 < n_pass; ++ps) {
         kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
         kp.first_pass = ps == 0; kp.last_pass = 0; kp.no_check = (bounds[ps + 1] - bounds[ps] <= P.grid) ? 1 : 0;
         rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
         if (rc) return rc;
-        rc = launch_seed_tau_lists(cand, k2t_cnt, P.grid, kp.nq_pad, P.cap, P.k_fetch, tau_g, static_cast<int>(bn), stream);
+        const int m = std::min(P.k_fetch, sample_rank(P.k_fetch, bounds[ps + 1], P.n_tiles));
+        rc = launch_seed_tau_lists(cand, k2t_cnt, P.grid, kp.nq_pad, P.cap, m, tau_g, static_cast<int>(bn), stream);
         if (rc) return rc;
         idx->stats.kernel_launches += 2;
       }
       kp.tile_begin = bounds[n_pass - 1]; kp.tile_end = P.n_tiles;
       kp.first_pass = n_pass == 1; kp.last_pass = 1; kp.no_check = 0;
+      if (n_pass > 1) {
+        rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
+        if (rc) return rc;
+        uint32_t* flag = tau_g + 3 * nq_pad + 8;
+        rc = launch_verify_counts(qcnt, tau_g, bn, static_cast<int>(std::min<int64_t>(P.k_fetch, idx->n)), flag, stream);
+        if (rc) return rc;
+        idx->stats.kernel_launches += 2;
+        // the fall-back launch: everything again from empty lists, for the queries the verification reset (all others: tau = +inf)
+        kp.tile_begin = 0; kp.first_pass = 1; kp.run_flag = flag;
+      }
       rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
@@ -866,7 +884,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       // them) leave in tau_g the score of a rank chosen so that -- except with probability ~e^-30 per query -- at least k' rows of
       // the whole corpus beat it; the main pass over the other tiles then keeps ~3 k' candidates per query instead of
       // k' ln(N / k') per owner.  The counts are verified afterwards; a query that came back short is searched again.
-      kp.perm_s = kp.perm_ns = kp.perm_s0 = kp.perm_n0 = 0;
+      kp.perm = TilePerm();
       kp.run_flag = nullptr;
       kp.prof = tau_g + 3 * nq_pad + 16;
       struct Pass { int64_t begin, end; int k; int est_only; };
@@ -877,16 +895,16 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
         const int64_t s1 = std::max(2, env_int("NXF_K1_EST_S1", 16)), s0 = std::max(2, env_int("NXF_K1_EST_S0", 16));
         const bool est = (est_env >= 0 ? est_env != 0 : true) && P.n_tiles >= 4 * s1 * s0 && kp.debug == 0;
         if (est) {
-          kp.perm_s = s1; kp.perm_ns = ceil_div64(P.n_tiles, s1);
-          kp.perm_s0 = s0; kp.perm_n0 = ceil_div64(kp.perm_ns, s0);
+          kp.perm.s = s1; kp.perm.ns = ceil_div64(P.n_tiles, s1);
+          kp.perm.s0 = s0; kp.perm.n0 = ceil_div64(kp.perm.ns, s0);
           // estimate-only pass: a few tiles per cluster (so that no row fills its buffer), only slice maxima are recorded; it spares
           // the first sample pass the cost of starting from -inf (every score appended, every row pruned after its first tile)
           const int64_t clusters = grid / P.cta_group;
-          const int64_t n_e = std::max<int64_t>(2, std::min<int64_t>(std::min<int64_t>(16, kp.perm_n0), 7 * clusters / std::max(kp.num_qt, 1)));
+          const int64_t n_e = std::max<int64_t>(2, std::min<int64_t>(std::min<int64_t>(16, kp.perm.n0), 7 * clusters / std::max(kp.num_qt, 1)));
           passes[n_pass++] = {0, n_e, std::min(P.k_fetch, sample_rank(P.k_fetch, n_e, P.n_tiles)), 1};
-          passes[n_pass++] = {0, kp.perm_n0, std::min(P.k_fetch, sample_rank(P.k_fetch, kp.perm_n0, P.n_tiles)), 0};
-          passes[n_pass++] = {kp.perm_n0, kp.perm_ns, std::min(P.k_fetch, sample_rank(P.k_fetch, kp.perm_ns, P.n_tiles)), 0};
-          passes[n_pass++] = {kp.perm_ns, P.n_tiles, P.k_fetch, 0};
+          passes[n_pass++] = {0, kp.perm.n0, std::min(P.k_fetch, sample_rank(P.k_fetch, kp.perm.n0, P.n_tiles)), 0};
+          passes[n_pass++] = {kp.perm.n0, kp.perm.ns, std::min(P.k_fetch, sample_rank(P.k_fetch, kp.perm.ns, P.n_tiles)), 0};
+          passes[n_pass++] = {kp.perm.ns, P.n_tiles, P.k_fetch, 0};
         } else {
           passes[n_pass++] = {0, P.n_tiles, P.k_fetch, 0};
         }

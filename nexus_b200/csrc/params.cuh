@@ -22,6 +22,27 @@ struct KxParams {
   SinkParams sink;
 };
 
+// Virtual -> physical order of the corpus tiles (DESIGN.md "sampled thresholds"): the first ns virtual tiles are the physical
+// tiles 0, s, 2s, ... -- of those, every s0-th comes first (n0 tiles) -- then all the others in order.  s <= 1: identity.
+struct TilePerm {
+  int64_t s = 0, ns = 0, s0 = 0, n0 = 0;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ int64_t perm_tile(const TilePerm& tp, int64_t v) {
+  if (tp.s <= 1) return v;
+  if (v >= tp.ns) {  // the j-th tile that is not a multiple of s
+    const int64_t j = v - tp.ns;
+    return j + j / (tp.s - 1) + 1;
+  }
+  int64_t i = v;  // index among the multiples of s
+  if (tp.s0 > 1) {
+    if (v < tp.n0) i = v * tp.s0;
+    else { const int64_t j = v - tp.n0; i = j + j / (tp.s0 - 1) + 1; }
+  }
+  return i * tp.s;
+}
+#endif
+
 struct K1Params {
   int64_t n;    // corpus rows
   int64_t nq;   // query rows
@@ -30,9 +51,7 @@ struct K1Params {
                 // segments of a tile are (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
   int num_qt;   // query tiles of 128*CG rows (<= number of clusters)
   int64_t tile_begin, tile_end;  // (virtual) corpus tiles [begin, end) of this pass (a search is 1-3 passes: sample, sample, rest)
-  // virtual -> physical tile order (DESIGN.md "sampled thresholds"): the first perm_ns virtual tiles are the physical tiles
-  // 0, s, 2s, ... (of those, every s0-th comes first: perm_n0 tiles), then all the others in order.  perm_s <= 1: identity
-  int64_t perm_s, perm_ns, perm_s0, perm_n0;
+  TilePerm perm;
   const uint32_t* run_flag;  // not NULL: the launch does nothing unless *run_flag != 0 (the fall-back pass after a failed verification)
   // end of every pass: each row's candidates (its sink.k best if it holds more) are appended to the query's arena slice
   int round_tiles;     // corpus tiles per round (the L2-resident window)
@@ -71,7 +90,9 @@ struct K2TParams {
   int check_every;  // tiles between two buffer-overflow checks (cap = 2k' + 2*128*check_every)
   // a search is 1-3 launches over consecutive tile ranges (DESIGN.md "K2T, threshold seeding"); the per-(CTA, query) lists and
   // their counts stay in global memory between launches
-  int64_t tile_begin, tile_end;  // this launch streams corpus tiles [tile_begin, tile_end), CTA b takes tile_begin + b + i * grid
+  int64_t tile_begin, tile_end;  // this launch streams (virtual) corpus tiles [tile_begin, tile_end), CTA b takes tile_begin + b + i * grid
+  TilePerm perm;
+  const uint32_t* run_flag;  // not NULL: the launch does nothing unless *run_flag != 0 (fall-back after a failed verification)
   uint32_t* cnt_g;  // [grid][nq_pad] list lengths carried from launch to launch
   int first_pass;   // lists start empty
   int last_pass;    // lists are reduced to k' and flushed to the arena at the end (else: lengths stored to cnt_g)

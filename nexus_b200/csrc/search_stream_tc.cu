@@ -116,6 +116,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   int* cnt_s = reinterpret_cast<int*>(tau_s + MAX_NQ);      // [MAX_NQ]
   uint32_t* hist = reinterpret_cast<uint32_t*>(cnt_s + MAX_NQ);
 
+  if (p.run_flag != nullptr && ld_relaxed_u32(p.run_flag) == 0u) return;  // uniform over the grid: written by an earlier kernel
   const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
   const unsigned lane = lane_id();
   const int64_t t_first = p.tile_begin + blockIdx.x;  // this CTA's tiles: t_first, t_first + grid, ... < t_end
@@ -150,7 +151,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       int s = 0;
       uint32_t ph = 0;
       for (int64_t t = t_first; t < t_end; t += gridDim.x) {
-        const int32_t row0 = static_cast<int32_t>(t * BLOCK_M);
+        const int32_t row0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_M);
         for (int kb = 0; kb < p.kblocks; ++kb) {
           mbar_wait(&empty[s], ph ^ 1);
           mbar_expect_tx(&full[s], A_BYTES);
@@ -215,7 +216,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 
     for (int64_t t = t_first; t < t_end; t += gridDim.x, ++iter) {
       const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
-      const int64_t row = t * BLOCK_M + et;
+      const int64_t row = perm_tile(p.perm, t) * BLOCK_M + et;
       const bool row_ok = row < p.n;
       const float hn = (L2 && row_ok) ? p.half_norm[row] : 0.f;
       mbar_wait(&tfull[b], bph);

@@ -147,21 +147,6 @@ __device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0,
   return rp;
 }
 
-// virtual -> physical corpus tile (K1Params::perm_*): sample tiles first, spread evenly over the corpus
-__device__ __forceinline__ int64_t phys_tile(const K1Params& p, int64_t v) {
-  if (p.perm_s <= 1) return v;
-  if (v >= p.perm_ns) {  // the j-th tile that is not a multiple of s
-    const int64_t j = v - p.perm_ns;
-    return j + j / (p.perm_s - 1) + 1;
-  }
-  int64_t i = v;  // index among the multiples of s
-  if (p.perm_s0 > 1) {
-    if (v < p.perm_n0) i = v * p.perm_s0;
-    else { const int64_t j = v - p.perm_n0; i = j + j / (p.perm_s0 - 1) + 1; }
-  }
-  return i * p.perm_s;
-}
-
 template <int CG, bool BF16>
 __global__ void __launch_bounds__(k1::THREADS, 1)
 k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K1Params p) {
@@ -222,7 +207,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           const int64_t lo = pos - qt * rp.R, hi = min(rp.b - qt * rp.R, rp.R);
           const int32_t q_row0 = static_cast<int32_t>((qt * CG + rank) * BLOCK_M);
           for (int64_t t = r0 + lo; t < r0 + hi; ++t) {
-            const int32_t c_row0 = static_cast<int32_t>(phys_tile(p, t) * BLOCK_N + rank * C::LOAD_N);
+            const int32_t c_row0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_N + rank * C::LOAD_N);
             for (int kb = 0; kb < p.kblocks; ++kb) {
               // column (in elements) of this K block in the query / corpus rows; split storage walks (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
               int32_t q_col = kb * BLOCK_K, c_col = kb * BLOCK_K;
@@ -340,7 +325,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
           mbar_wait(&tfull[as], aph);
           tc_fence_after();
-          const int32_t col0 = static_cast<int32_t>(phys_tile(p, t) * BLOCK_N);
+          const int32_t col0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_N);
           // slow-path epilogue: the last corpus tile (rows past n are TMA zero fill) or the L2 metric
           const bool adj = (col0 + BLOCK_N > n_rows) || (p.half_norm != nullptr);
           const uint32_t tbase = taddr + as * BLOCK_N;

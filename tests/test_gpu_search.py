@@ -136,6 +136,22 @@ def test_tensor_stream_kernel_seeded(store, case):
         assert st["kernel_launches"] >= 6    # 2 converts, seed pass, seed threshold, main pass, merge
 
 
+def test_tensor_stream_kernel_sampled_thresholds_fallback():
+    """Adversarial corpus for K2T's sample (148 CTAs, 2344 tiles of 128 rows -> every 15th tile is a sample tile): all rows that
+    matter lie in sample tiles, the sampled threshold is far too high, every query must go through the fall-back launch."""
+    n, d, q, k = 300000, 64, 100, 100
+    rng = np.random.default_rng(6)
+    c = (0.05 * rng.standard_normal((n, d))).astype(np.float32)
+    x = rng.standard_normal((q, d)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    n_tiles = (n + 127) // 128
+    stride = n_tiles // 148
+    hot = np.flatnonzero((np.arange(n) // 128) % stride == 0)
+    c[hot] += x[rng.integers(0, q, size=hot.size)] * rng.uniform(0.5, 1.0, size=(hot.size, 1)).astype(np.float32)
+    run_and_check(c, x, k, store="bf16", path="auto", rtol=1e-5, expect_path="tstream", min_recall=0.999)
+    run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, expect_path="tstream", min_recall=0.999)
+
+
 def test_tensor_stream_falls_back_when_queries_do_not_fit():
     """128 queries x 1536 dims = 393 KB of resident queries: K2T is not eligible, the search is served by K1."""
     c, x = gen_inputs(6000, 1536, 128, seed=9)

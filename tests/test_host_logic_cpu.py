@@ -97,3 +97,32 @@ def test_install_as_faiss_registers_modules():
                 sys.modules.pop(k, None)
             else:
                 sys.modules[k] = v
+
+
+def _perm_tile(s, ns, s0, n0, v):
+    """Python restatement of perm_tile() in nexus_b200/csrc/params.cuh (the sample-first order of the corpus tiles)."""
+    if s <= 1:
+        return v
+    if v >= ns:
+        j = v - ns
+        return j + j // (s - 1) + 1
+    i = v
+    if s0 > 1:
+        if v < n0:
+            i = v * s0
+        else:
+            j = v - n0
+            i = j + j // (s0 - 1) + 1
+    return i * s
+
+
+@pytest.mark.parametrize("n_tiles,s,s0", [(1024, 16, 16), (4297, 16, 16), (34375, 16, 16), (78125, 31, 17), (1000, 6, 1), (37, 4, 3), (2, 2, 2)])
+def test_tile_permutation_is_a_bijection_with_spread_samples(n_tiles, s, s0):
+    ns = -(-n_tiles // s)
+    n0 = -(-ns // s0) if s0 > 1 else ns
+    phys = [_perm_tile(s, ns, s0, n0, v) for v in range(n_tiles)]
+    assert sorted(phys) == list(range(n_tiles))
+    assert all(p % s == 0 for p in phys[:ns])                     # the sample: every s-th tile
+    if s0 > 1:
+        assert all(p % (s * s0) == 0 for p in phys[:n0])          # its first level: every (s*s0)-th tile
+    assert phys[ns:] == sorted(phys[ns:])                         # everything else in corpus order
