@@ -28,18 +28,21 @@ struct TilePerm {
   int64_t s = 0, ns = 0, s0 = 0, n0 = 0;
 };
 #ifdef __CUDACC__
-__device__ __forceinline__ int64_t perm_tile(const TilePerm& tp, int64_t v) {
-  if (tp.s <= 1) return v;
-  if (v >= tp.ns) {  // the j-th tile that is not a multiple of s
-    const int64_t j = v - tp.ns;
-    return j + j / (tp.s - 1) + 1;
+__device__ __forceinline__ int64_t perm_tile(const TilePerm& tp, int64_t v64) {
+  if (tp.s <= 1) return v64;
+  // tile indices fit 32 bits (< 2^31 rows per device): 32-bit divisions
+  const uint32_t v = static_cast<uint32_t>(v64), s = static_cast<uint32_t>(tp.s), ns = static_cast<uint32_t>(tp.ns);
+  if (v >= ns) {  // the j-th tile that is not a multiple of s
+    const uint32_t j = v - ns;
+    return static_cast<int64_t>(j + j / (s - 1u) + 1u);
   }
-  int64_t i = v;  // index among the multiples of s
+  uint32_t i = v;  // index among the multiples of s
   if (tp.s0 > 1) {
-    if (v < tp.n0) i = v * tp.s0;
-    else { const int64_t j = v - tp.n0; i = j + j / (tp.s0 - 1) + 1; }
+    const uint32_t s0 = static_cast<uint32_t>(tp.s0), n0 = static_cast<uint32_t>(tp.n0);
+    if (v < n0) i = v * s0;
+    else { const uint32_t j = v - n0; i = j + j / (s0 - 1u) + 1u; }
   }
-  return i * tp.s;
+  return static_cast<int64_t>(i) * tp.s;
 }
 #endif
 
