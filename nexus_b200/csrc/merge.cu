@@ -97,6 +97,36 @@ __device__ __forceinline__ int next_pow2(int v) {
   return p;
 }
 
+// 8 consecutive stored elements (16-byte aligned) as fp32
+template <typename T>
+__device__ __forceinline__ void load8_f32(const T* __restrict__ p, float (&out)[8]);
+template <>
+__device__ __forceinline__ void load8_f32<float>(const float* __restrict__ p, float (&out)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  out[0] = a.x; out[1] = a.y; out[2] = a.z; out[3] = a.w; out[4] = b.x; out[5] = b.y; out[6] = b.z; out[7] = b.w;
+}
+template <>
+__device__ __forceinline__ void load8_f32<__nv_bfloat16>(const __nv_bfloat16* __restrict__ p, float (&out)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    out[2 * i] = __uint_as_float(w[i] << 16);
+    out[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+  }
+}
+template <>
+__device__ __forceinline__ void load8_f32<__half>(const __half* __restrict__ p, float (&out)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(h[i]);
+    out[2 * i] = f.x;
+    out[2 * i + 1] = f.y;
+  }
+}
+
 // ---- arena merge (+ optional rescore) ---------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaParams p) {
@@ -120,8 +150,8 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
   const bool need_q = p.rescore || p.metric == NXF_METRIC_L2;
   if (need_q) {
     float part = 0.f;
-    for (int d = tid; d < p.dim; d += mg::THREADS) {
-      const float v = p.q[qi * p.ldq + d];
+    for (int d = tid; d < static_cast<int>(p.ld); d += mg::THREADS) {  // ldq >= ld and both are zero padded past dim
+      const float v = d < p.dim ? p.q[qi * p.ldq + d] : 0.f;
       q_s[d] = v;
       part += v * v;
     }
@@ -160,25 +190,40 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
   }
   __syncthreads();
 
-  // ---- exact fp32 re-score: one warp per candidate ----
+  // ---- exact fp32 re-score: one warp per candidate, two candidates in flight per warp, 16-byte loads ----
+  // (rows are ld = 64k elements long and zero padded, q_s holds ld entries: no tail handling)
   if (p.rescore) {
     const T* __restrict__ corpus = reinterpret_cast<const T*>(p.corpus);
     const int warp = tid >> 5, lane = tid & 31;
-    for (int c = warp; c < keep; c += mg::THREADS / 32) {
-      const int32_t row = ent[c].row;
-      const T* r = corpus + static_cast<int64_t>(row) * p.ld;
-      float dot = 0.f, nn = 0.f;
-      for (int d = lane; d < p.dim; d += 32) {
-        const float v = to_f32<T>(r[d]);
-        dot = fmaf(q_s[d], v, dot);
-        nn = fmaf(v, v, nn);
+    const int ld = static_cast<int>(p.ld);
+    constexpr int NW = mg::THREADS / 32;
+    for (int c = warp; c < keep; c += 2 * NW) {
+      const int c2 = c + NW;
+      const bool two = c2 < keep;
+      const T* r0 = corpus + static_cast<int64_t>(ent[c].row) * p.ld;
+      const T* r1 = corpus + static_cast<int64_t>(ent[two ? c2 : c].row) * p.ld;
+      float dot0 = 0.f, nn0 = 0.f, dot1 = 0.f, nn1 = 0.f;
+      for (int d0 = lane * 8; d0 < ld; d0 += 256) {
+        float a[8], b[8];
+        load8_f32<T>(r0 + d0, a);
+        load8_f32<T>(r1 + d0, b);
+        const float4 q0 = *reinterpret_cast<const float4*>(q_s + d0), q1 = *reinterpret_cast<const float4*>(q_s + d0 + 4);
+        const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          dot0 = fmaf(qv[e], a[e], dot0); nn0 = fmaf(a[e], a[e], nn0);
+          dot1 = fmaf(qv[e], b[e], dot1); nn1 = fmaf(b[e], b[e], nn1);
+        }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        dot += __shfl_xor_sync(kFullMask, dot, o);
-        nn += __shfl_xor_sync(kFullMask, nn, o);
+        dot0 += __shfl_xor_sync(kFullMask, dot0, o); nn0 += __shfl_xor_sync(kFullMask, nn0, o);
+        dot1 += __shfl_xor_sync(kFullMask, dot1, o); nn1 += __shfl_xor_sync(kFullMask, nn1, o);
       }
-      if (lane == 0) ent[c].score = (p.metric == NXF_METRIC_L2) ? (dot - 0.5f * nn) : dot;
+      if (lane == 0) {
+        ent[c].score = (p.metric == NXF_METRIC_L2) ? (dot0 - 0.5f * nn0) : dot0;
+        if (two) ent[c2].score = (p.metric == NXF_METRIC_L2) ? (dot1 - 0.5f * nn1) : dot1;
+      }
     }
     __syncthreads();
   }
@@ -214,7 +259,7 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream) {
   if (nq <= 0) return NXF_OK;
   const bool need_q = p.rescore || p.metric == NXF_METRIC_L2;
-  const size_t smem = static_cast<size_t>(mg::MAXK) * 8 + (need_q ? static_cast<size_t>(p.dim) * 4 : 0);
+  const size_t smem = static_cast<size_t>(mg::MAXK) * 8 + (need_q ? static_cast<size_t>(p.ld) * 4 : 0);
   if (smem > 200 * 1024) { set_error("merge: dim %d too large for the re-score stage", p.dim); return NXF_EUNSUPPORTED; }
 #define NXF_LAUNCH_MERGE(T)                                                                                          \
   do {                                                                                                               \
