@@ -16,7 +16,14 @@
 
 namespace nxf {
 
+#ifndef NXF_POOL_CTAS
+#define NXF_POOL_CTAS (6 * 3 * 148)
+#endif
+#ifndef NXF_POOL_UNROLL
+#define NXF_POOL_UNROLL 8
+#endif
 namespace k0 {
+constexpr int MEAN_UNROLL = NXF_POOL_UNROLL;
 constexpr int THREADS = 256;
 constexpr int MAX_GROUPS = 8;
 }  // namespace k0
@@ -170,10 +177,159 @@ __global__ void __launch_bounds__(k0::THREADS) pool_norm_kernel(const T* __restr
   for (int64_t h = tid; h < H; h += k0::THREADS) ob[h] = from_f32<O>(normalize ? vals[h] * scale : vals[h]);
 }
 
+// ---- mean pooling at the HBM roofline ------------------------------------------------------------
+// One CTA per batch row cannot fill 148 SMs (B is 64..256 where L is long), so L is split over `splits` CTAs per row:
+// grid (splits, B), block = G groups x nvec threads (thread (g, v) owns vector column v and positions l0+g, l0+g+G, ...;
+// consecutive threads read consecutive 16-byte vectors of one position, masked positions are skipped).  Every CTA
+// writes its fp32 partial sums to a workspace [B][splits][H]; the last CTA of a row to arrive (one atomic counter per
+// row) adds the partials in a fixed order -- results do not depend on the arrival order --, divides by the mask sum,
+// normalises, casts and stores.
+template <typename T, typename O, int VEC>
+__global__ void __launch_bounds__(512) pool_mean_split_kernel(const T* __restrict__ hidden, const int64_t* __restrict__ mask, int64_t L,
+                                                              int64_t H, int normalize, float eps, O* __restrict__ out, int G,
+                                                              float* __restrict__ partial, unsigned long long* __restrict__ den_g,
+                                                              unsigned int* __restrict__ counter) {
+  extern __shared__ __align__(16) float vals[];  // [G][H], reused as [H] by the finalising CTA
+  __shared__ float red_f[16];
+  __shared__ unsigned int s_last;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int splits = gridDim.x, sp = blockIdx.x;
+  const int64_t b = blockIdx.y;
+  const int nvec = static_cast<int>(H / VEC);
+  const int64_t lc = (L + splits - 1) / splits;
+  const int64_t l0 = sp * lc, l1 = min(L, l0 + lc);
+  const T* hb = hidden + b * L * H;
+  const int64_t* mb = mask + b * L;
+
+  __shared__ int s_lo, s_hi;
+  if (tid == 0) { s_lo = INT_MAX; s_hi = -1; }
+  __syncthreads();
+  unsigned long long wsum = 0;
+  int lo = INT_MAX, hi = -1;  // first / last unmasked position of the slice, relative to l0
+  for (int64_t l = l0 + tid; l < l1; l += nthr) {
+    const int64_t w = mb[l];
+    wsum += static_cast<unsigned long long>(w);
+    if (w != 0) { lo = min(lo, static_cast<int>(l - l0)); hi = max(hi, static_cast<int>(l - l0)); }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xFFFFFFFFu, wsum, o);
+  lo = __reduce_min_sync(0xFFFFFFFFu, lo);
+  hi = __reduce_max_sync(0xFFFFFFFFu, hi);
+  if ((tid & 31) == 0) {
+    if (wsum != 0) atomicAdd(&den_g[b], wsum);
+    atomicMin(&s_lo, lo);
+    atomicMax(&s_hi, hi);
+  }
+  __syncthreads();
+  const int64_t n0 = l0 + s_lo, n1 = (s_hi >= 0) ? l0 + s_hi + 1 : n0;  // empty when the whole slice is masked
+
+  const int g = tid / nvec, v0 = tid - g * nvec;  // threads beyond G*nvec (block rounded up to a warp) idle
+  if (g < G) {
+    for (int v = v0; v < nvec; v += nvec) {  // block covers all vector columns when nvec <= 512 (H <= 4096 for 16-bit types)
+      float acc[VEC];
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) acc[e] = 0.f;
+      const T* col = hb + static_cast<int64_t>(v) * VEC;
+      // unconditional loads over [n0, n1) -- the part of the slice between its first and last unmasked position -- so that the
+      // unrolled loads are independent of the mask words; a masked position inside that range contributes h * 0 like the
+      // reference's h * mask.float()
+#pragma unroll k0::MEAN_UNROLL
+      for (int64_t l = n0 + g; l < n1; l += G) {
+#ifdef NXF_POOL_COND
+        const int64_t w = mb[l];
+        if (w != 0) {
+          float x[VEC];
+          VecLoad<T, VEC>::load(col + l * H, x);
+          const float wf = static_cast<float>(w);
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) acc[e] = fmaf(x[e], wf, acc[e]);
+        }
+#else
+        float x[VEC];
+        VecLoad<T, VEC>::load(col + l * H, x);
+        const float wf = static_cast<float>(mb[l]);
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) acc[e] = fmaf(x[e], wf, acc[e]);
+#endif
+      }
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) vals[static_cast<int64_t>(g) * H + v * VEC + e] = acc[e];
+    }
+  }
+  __syncthreads();
+  float* my_part = partial + (b * splits + sp) * H;
+  for (int64_t h = tid; h < H; h += nthr) {
+    float s = 0.f;
+    for (int gg = 0; gg < G; ++gg) s += vals[static_cast<int64_t>(gg) * H + h];
+    my_part[h] = s;
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(&counter[b], 1u) == static_cast<unsigned>(splits - 1)) ? 1u : 0u;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const float fden = static_cast<float>(static_cast<long long>(*reinterpret_cast<volatile unsigned long long*>(&den_g[b])));
+  float ss = 0.f;
+  for (int64_t h = tid; h < H; h += nthr) {
+    float s = 0.f;
+    for (int j = 0; j < splits; ++j) s += __ldcg(partial + (b * splits + j) * H + h);
+    s /= fden;  // 0/0 -> NaN for an empty mask, like the reference
+    vals[h] = s;
+    ss = fmaf(s, s, ss);
+  }
+  float scale = 1.f;
+  if (normalize) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xFFFFFFFFu, ss, o);
+    if ((tid & 31) == 0) red_f[tid >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+    for (int w = 0; w < (nthr + 31) / 32; ++w) tot += red_f[w];
+    const float nrm = sqrtf(tot);
+    scale = 1.f / (eps > 0.f ? fmaxf(nrm, eps) : nrm);
+  }
+  O* ob = out + b * H;
+  for (int64_t h = tid; h < H; h += nthr) ob[h] = from_f32<O>(normalize ? vals[h] * scale : vals[h]);
+}
+
+template <typename T, typename O, int VEC>
+static int launch_pool_mean_split(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int normalize, float eps,
+                                  void* out, cudaStream_t stream) {
+  const int nvec = static_cast<int>(H / VEC);
+  const int G = std::max(1, 512 / nvec);
+  const int threads = std::min(512, (G * nvec + 31) / 32 * 32);
+  // ~3 CTAs of this size are resident per SM: aim at >= 6 waves so that the last, partial wave costs little
+  int splits = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>((NXF_POOL_CTAS + B - 1) / B, std::max<int64_t>(1, L / 64))));
+  const size_t smem = static_cast<size_t>(G) * H * 4;
+  const size_t part_bytes = static_cast<size_t>(B) * splits * H * 4;
+  const size_t ctl_bytes = static_cast<size_t>(B) * 16;  // den (u64) + counter (u32), 16 bytes per row
+  unsigned char* ws = nullptr;
+  NXF_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&ws), part_bytes + ctl_bytes, stream));
+  unsigned long long* den = reinterpret_cast<unsigned long long*>(ws + part_bytes);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(ws + part_bytes + static_cast<size_t>(B) * 8);
+  cudaError_t e = cudaMemsetAsync(ws + part_bytes, 0, ctl_bytes, stream);
+  if (e == cudaSuccess) {
+    auto kern = pool_mean_split_kernel<T, O, VEC>;
+    if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e == cudaSuccess) {
+      kern<<<dim3(static_cast<unsigned>(splits), static_cast<unsigned>(B)), threads, smem, stream>>>(
+          (const T*)hidden, mask, L, H, normalize, eps, (O*)out, G, reinterpret_cast<float*>(ws), den, counter);
+      e = cudaGetLastError();
+    }
+  }
+  cudaFreeAsync(ws, stream);
+  NXF_CUDA(e);
+  return NXF_OK;
+}
+
 template <typename T, typename O, int VEC>
 static int launch_pool_t(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int pooling, int normalize, float eps,
                          void* out, cudaStream_t stream) {
   const int nvec = static_cast<int>(H / VEC);
+  // mean over vectorisable rows: the split kernel (any B fills the GPU); B <= 65535 is the grid's y limit
+  if (pooling == NXF_POOL_MEAN && VEC > 1 && nvec <= 512 && B <= 65535 && static_cast<size_t>(std::max(1, 512 / nvec)) * H * 4 <= 160 * 1024)
+    return launch_pool_mean_split<T, O, VEC>(hidden, mask, B, L, H, normalize, eps, out, stream);
   int groups = 1;
   if (pooling == NXF_POOL_MEAN) {
     groups = std::max(1, std::min(k0::MAX_GROUPS, k0::THREADS / std::max(1, std::min(nvec, k0::THREADS))));
