@@ -335,6 +335,16 @@ def run_ours(a):
         peak = peaks["bf16_tflops_sustained"]
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                 "frac_of_nominal_2250": achieved / 2250.0}
+    # measured DRAM traffic of the same kernel sequence (ncu --set full, committed under profiles/), single-GPU full-size runs only
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        kname = {"tensor": "k1_search_kernel", "stream": "k2_stream_kernel", "tstream": "k2t_stream_kernel", "exact": "kx_search_kernel"}.get(path, path)
+        ent = tr.get(f"{a.config}/{kname}")
+        if ent and world == 1 and not (a.n or a.nq or a.k):
+            roof["traffic"] = ent["bytes"]
+            roof["traffic_note"] = ent["note"]
+    except Exception:
+        pass
     roof.update({"kernel": {"tensor": "k1_search_kernel", "stream": "k2_stream_kernel", "tstream": "k2t_stream_kernel", "exact": "kx_search_kernel"}.get(path, path),
                  "kernel_ms": kern_ms, "kernel_launches_timed": st1["main_kernel_count"], "peak_source": peaks["source"],
                  "algorithmic_work": "2*Q*(N/G)*D FLOPs per launch" if not hbm_bound else "N*ld*sizeof(T) bytes per launch"})
