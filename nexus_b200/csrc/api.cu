@@ -716,7 +716,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   // ---- carve scratch (two passes: size, then pointers) ----
   const size_t qsz = dtype_size(q_dtype);
   unsigned char* base = nullptr;
-  float* q_f32 = nullptr; void* q16 = nullptr; void* q_src = nullptr; uint32_t* tau_g = nullptr; uint32_t* qcnt = nullptr; uint32_t* qlock = nullptr;
+  float* q_f32 = nullptr; void* q16 = nullptr; void* q_src = nullptr; uint32_t* tau_g = nullptr; uint32_t* qcnt = nullptr;
   Entry* arena = nullptr; Entry* cand = nullptr; float* o_scores = nullptr; int64_t* o_ids = nullptr; uint32_t* k2t_cnt = nullptr;
   const int64_t nq_pad = round_up64(batch, 256);
   for (int pass = 0; pass < 2; ++pass) {
@@ -725,9 +725,9 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     q_f32 = cv.take<float>(static_cast<size_t>(nq_pad) * idx->ld);
     q16 = (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld * (P.split ? 2 : 1))
                                                                     : nullptr;
-    tau_g = cv.take<uint32_t>(static_cast<size_t>(3 * nq_pad + 64));  // tau | qcnt | lock | K1 round counter
+    // tau | qcnt | 64 control words: [0..5] K1 round counters (one per pass), [8] verification flag, [16..23] debug cycle counters
+    tau_g = cv.take<uint32_t>(static_cast<size_t>(2 * nq_pad + 64));
     qcnt = tau_g ? tau_g + nq_pad : nullptr;
-    qlock = tau_g ? tau_g + 2 * nq_pad : nullptr;
     arena = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(batch * P.arena_stride, rem_arena)));
     cand = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(P.owners, 1)) * P.cap);
     k2t_cnt = P.path == NXF_PATH_TSTREAM ? cv.take<uint32_t>(static_cast<size_t>(std::max<int64_t>(P.owners, 1))) : nullptr;
@@ -763,7 +763,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       if (rc) return rc;
       idx->stats.kernel_launches++;
     }
-    NXF_CUDA(cudaMemsetAsync(tau_g, 0, static_cast<size_t>(3 * nq_pad + 64) * sizeof(uint32_t), stream));
+    NXF_CUDA(cudaMemsetAsync(tau_g, 0, static_cast<size_t>(2 * nq_pad + 64) * sizeof(uint32_t), stream));
 
     cudaEvent_t pe0 = nullptr, pe1 = nullptr;
     if (idx->profiling && P.path != NXF_PATH_NONE) {
@@ -773,7 +773,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     }
     const int64_t arena_stride = (P.path == NXF_PATH_TENSOR && bn < batch && rem_stride > 0) ? rem_stride : P.arena_stride;
     SinkParams sink;
-    sink.tau_g = tau_g; sink.qcnt = qcnt; sink.lock = qlock; sink.arena = arena; sink.cand = cand;
+    sink.tau_g = tau_g; sink.qcnt = qcnt; sink.arena = arena; sink.cand = cand;
     sink.arena_stride = arena_stride; sink.cap = P.cap; sink.k = P.k_fetch;
 
     if (P.path == NXF_PATH_STREAM) {
@@ -843,7 +843,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       if (n_pass > 1) {
         rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
         if (rc) return rc;
-        uint32_t* flag = tau_g + 3 * nq_pad + 8;
+        uint32_t* flag = tau_g + 2 * nq_pad + 8;
         rc = launch_verify_counts(qcnt, tau_g, bn, static_cast<int>(std::min<int64_t>(P.k_fetch, idx->n)), flag, stream);
         if (rc) return rc;
         idx->stats.kernel_launches += 2;
@@ -886,7 +886,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       // k' ln(N / k') per owner.  The counts are verified afterwards; a query that came back short is searched again.
       kp.perm = TilePerm();
       kp.run_flag = nullptr;
-      kp.prof = tau_g + 3 * nq_pad + 16;
+      kp.prof = tau_g + 2 * nq_pad + 16;
       struct Pass { int64_t begin, end; int k; int est_only; };
       Pass passes[4];
       int n_pass = 0;
@@ -914,7 +914,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
         kp.tile_begin = passes[ps].begin; kp.tile_end = passes[ps].end;
         kp.sink.k = passes[ps].k;
         kp.debug = user_debug | (passes[ps].est_only ? 128 : 0);
-        kp.sync_ctr = tau_g + 3 * nq_pad + ps;   // one round counter per pass (all zeroed above)
+        kp.sync_ctr = tau_g + 2 * nq_pad + ps;   // one round counter per pass (all zeroed above)
         rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
                      : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
         if (rc) return rc;
@@ -928,12 +928,12 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.debug = user_debug;
       if (n_pass > 1) {
         // verification + fall-back: the launch below returns at once unless some query holds fewer than min(k', n) candidates
-        uint32_t* flag = tau_g + 3 * nq_pad + 8;
+        uint32_t* flag = tau_g + 2 * nq_pad + 8;
         rc = launch_verify_counts(qcnt, tau_g, bn, static_cast<int>(std::min<int64_t>(P.k_fetch, idx->n)), flag, stream);
         if (rc) return rc;
         kp.tile_begin = 0; kp.tile_end = P.n_tiles; kp.sink.k = P.k_fetch;
         kp.run_flag = flag;
-        kp.sync_ctr = tau_g + 3 * nq_pad + 5;
+        kp.sync_ctr = tau_g + 2 * nq_pad + 5;
         rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
                      : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
         if (rc) return rc;
@@ -943,7 +943,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
 
     if (P.path == NXF_PATH_TENSOR && (env_int("NXF_K1_DEBUG", 0) & 32)) {
       unsigned long long h[4] = {0, 0, 0, 0};
-      NXF_CUDA(cudaMemcpyAsync(h, tau_g + 3 * nq_pad + 16, sizeof(h), cudaMemcpyDeviceToHost, stream));
+      NXF_CUDA(cudaMemcpyAsync(h, tau_g + 2 * nq_pad + 16, sizeof(h), cudaMemcpyDeviceToHost, stream));
       NXF_CUDA(cudaStreamSynchronize(stream));
       fprintf(stderr, "[nxf K1 prof] prunes=%llu prune_cycles/warp=%.0f end_merge_cycles/warp=%.0f cycles/prune=%.0f (epilogue warps %llu)\n", h[0],
               h[3] ? double(h[1]) / h[3] : 0.0, h[3] ? double(h[2]) / h[3] : 0.0, h[0] ? double(h[1]) / h[0] : 0.0, h[3]);

@@ -387,7 +387,7 @@ __global__ void __launch_bounds__(256) select_tau_kernel(Entry* __restrict__ are
   int n = static_cast<int>(min(static_cast<int64_t>(qcnt[q]), arena_stride));
   __syncwarp();
   if (n > m) {
-    const uint32_t kth = warp_prune(arena + q * arena_stride, n, m, nullptr);
+    const uint32_t kth = warp_prune(arena + q * arena_stride, n, m);
     if (lane == 0) atomicMax(&tau_g[q], kth);
     n = m;
   }

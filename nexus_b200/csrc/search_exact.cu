@@ -8,7 +8,7 @@
 // Work decomposition: unit = (corpus chunk c, query tile qt), qt fastest so that co-running CTAs
 // read the same corpus rows (L2 reuse).  A CTA owns 128 query rows for the whole unit: per-row
 // threshold/count live in shared memory, candidates go to a CTA-private global buffer, and a row is
-// pruned by one warp (radix select) when its buffer could overflow during the next tile.
+// pruned by one warp (bitwise-descent select, select.cuh) when its buffer could overflow during the next tile.
 #include "params.cuh"
 
 namespace nxf {
@@ -28,7 +28,6 @@ __global__ void __launch_bounds__(kx::THREADS) kx_search_kernel(KxParams p) {
   __shared__ __align__(16) float Bs[BK][BN + PAD];
   __shared__ float tau_s[BM];
   __shared__ int cnt_s[BM];
-  __shared__ uint32_t hist_s[THREADS / 32][256];
   __shared__ int any_prune_s;
 
   const int tid = threadIdx.x;
@@ -126,7 +125,7 @@ __global__ void __launch_bounds__(kx::THREADS) kx_search_kernel(KxParams p) {
         for (int row = warp; row < BM; row += THREADS / 32) {
           const int n = cnt_s[row];
           if (n > cap - BN && n > k) {
-            const uint32_t kth = warp_prune(my_cand + static_cast<int64_t>(row) * cap, n, k, hist_s[warp]);
+            const uint32_t kth = warp_prune(my_cand + static_cast<int64_t>(row) * cap, n, k);
             if (lane == 0) {
               cnt_s[row] = k;
               tau_s[row] = fmaxf(tau_s[row], okey_inv(kth));
@@ -148,7 +147,7 @@ __global__ void __launch_bounds__(kx::THREADS) kx_search_kernel(KxParams p) {
       Entry* buf = my_cand + static_cast<int64_t>(row) * cap;
       if (q0 + row >= p.nq) continue;
       if (n > k) {
-        const uint32_t kth = warp_prune(buf, n, k, hist_s[warp]);
+        const uint32_t kth = warp_prune(buf, n, k);
         if (lane == 0) atomicMax(&p.sink.tau_g[q0 + row], kth);
         n = k;
       }

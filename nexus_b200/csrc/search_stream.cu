@@ -11,7 +11,7 @@
 //   warps 0..7  consumers: warp w owns rows [w*RW, (w+1)*RW) of the stage; lanes split each row in
 //               16-byte chunks (conflict-free LDS.128), fp32 FMA against the queries held in shared
 //               memory, a transposing butterfly reduce leaves one (row, query) score per lane pair,
-//               then the streaming top-k sink (threshold filter -> append -> warp radix prune).
+//               then the streaming top-k sink (threshold filter -> append -> warp prune, select.cuh).
 #include "params.cuh"
 
 namespace nxf {
@@ -101,7 +101,6 @@ __global__ void __launch_bounds__(k2::THREADS, 1) k2_stream_kernel(K2Params p) {
   float* q_s = reinterpret_cast<float*>(smem + stage_bytes * p.stages);                 // [NQ][ld]
   uint64_t* full = reinterpret_cast<uint64_t*>(q_s + static_cast<int64_t>(NQ) * p.ld);  // [stages]
   uint64_t* empty = full + MAX_STAGES;
-  uint32_t* hist = reinterpret_cast<uint32_t*>(empty + MAX_STAGES);                     // [CONSUMER_WARPS][256]
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -140,7 +139,6 @@ __global__ void __launch_bounds__(k2::THREADS, 1) k2_stream_kernel(K2Params p) {
   // --------------------------------- consumers ---------------------------------
   const int cap = p.sink.cap;
   const int k = p.sink.k;
-  uint32_t* my_hist = hist + warp * 256;
   Entry* my_cand = p.sink.cand + (static_cast<int64_t>(blockIdx.x) * CONSUMER_WARPS + warp) * NQ * cap;
   float tau[NQ];
   int cnt[NQ];
@@ -220,7 +218,7 @@ __global__ void __launch_bounds__(k2::THREADS, 1) k2_stream_kernel(K2Params p) {
           cnt[qi] += __popc(m);
           __syncwarp();
           if (cnt[qi] > cap - RW) {  // the next stage could add RW more
-            const uint32_t kth = warp_prune(buf, cnt[qi], k, my_hist);
+            const uint32_t kth = warp_prune(buf, cnt[qi], k);
             cnt[qi] = k;
             if (lane == 0) atomicMax(&p.sink.tau_g[qi], kth);
             tau[qi] = fmaxf(tau[qi], okey_inv(kth));
@@ -240,7 +238,7 @@ __global__ void __launch_bounds__(k2::THREADS, 1) k2_stream_kernel(K2Params p) {
     if (qi >= p.nq) continue;
     Entry* buf = my_cand + static_cast<int64_t>(qi) * cap;
     int n = cnt[qi];
-    if (n > k) { warp_prune(buf, n, k, my_hist); n = k; }
+    if (n > k) { warp_prune(buf, n, k); n = k; }
     __syncwarp();
     warp_flush(p.sink, buf, n, qi);
   }
@@ -248,8 +246,7 @@ __global__ void __launch_bounds__(k2::THREADS, 1) k2_stream_kernel(K2Params p) {
 
 size_t k2_smem_bytes(int64_t ld, int elem_size, int nq_t, int rw, int stages) {
   const int64_t stage_bytes = ld * elem_size * k2::CONSUMER_WARPS * rw;
-  return static_cast<size_t>(stage_bytes * stages + static_cast<int64_t>(nq_t) * ld * 4 + 2 * k2::MAX_STAGES * 8 +
-                             k2::CONSUMER_WARPS * 256 * 4);
+  return static_cast<size_t>(stage_bytes * stages + static_cast<int64_t>(nq_t) * ld * 4 + 2 * k2::MAX_STAGES * 8);
 }
 
 template <typename T, int NQ, int RW>

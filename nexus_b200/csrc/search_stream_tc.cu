@@ -29,8 +29,8 @@ constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB per stage
 constexpr int MAX_STAGES = 12;
 constexpr int MAX_TBUF = 8;
 constexpr int MAX_NQ = 128;
-// shared memory after the 1024-aligned (queries | ring): barriers, tau, counts, prune histograms
-constexpr int TAIL_BYTES = (2 * MAX_STAGES + 2 * MAX_TBUF + 2) * 8 + 16 + MAX_NQ * 4 * 2 + 4 * 256 * 4;
+// shared memory after the 1024-aligned (queries | ring): barriers, tau, counts
+constexpr int TAIL_BYTES = (2 * MAX_STAGES + 2 * MAX_TBUF + 2) * 8 + 16 + MAX_NQ * 4 * 2;
 }  // namespace k2t
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
@@ -114,7 +114,6 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   uint32_t* tmem_ptr_s = reinterpret_cast<uint32_t*>(qfull + 2);
   float* tau_s = reinterpret_cast<float*>(tmem_ptr_s + 4);  // [MAX_NQ]
   int* cnt_s = reinterpret_cast<int*>(tau_s + MAX_NQ);      // [MAX_NQ]
-  uint32_t* hist = reinterpret_cast<uint32_t*>(cnt_s + MAX_NQ);
 
   if (p.run_flag != nullptr && ld_relaxed_u32(p.run_flag) == 0u) return;  // uniform over the grid: written by an earlier kernel
   const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
@@ -202,7 +201,6 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int ew = warp - EPI_WARP0;
     const int et = ew * 32 + static_cast<int>(lane);  // 0..127: epilogue thread == corpus row within the tile == query it looks after
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
-    uint32_t* my_hist = hist + ew * 256;
     const int cap = p.sink.cap;
     const int k = p.sink.k;
     Entry* cta_cand = p.sink.cand + static_cast<int64_t>(blockIdx.x) * p.nq_pad * cap;  // [nq_pad][cap]
@@ -258,7 +256,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         for (int qi = ew; qi < p.nq; qi += 4) {  // warp w prunes queries w, w+4, ...
           const int n_q = cnt_s[qi];
           if (n_q > full_mark && n_q > k) {
-            const uint32_t kth = warp_prune(cta_cand + static_cast<int64_t>(qi) * cap, n_q, k, my_hist);
+            const uint32_t kth = warp_prune(cta_cand + static_cast<int64_t>(qi) * cap, n_q, k);
             if (lane == 0) {
               cnt_s[qi] = k;
               tau_s[qi] = fmaxf(tau_s[qi], okey_inv(kth));
@@ -286,7 +284,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         int n_q = cnt_s[qi];
         Entry* buf = cta_cand + static_cast<int64_t>(qi) * cap;
         if (n_q > k) {
-          const uint32_t kth = warp_prune(buf, n_q, k, my_hist);
+          const uint32_t kth = warp_prune(buf, n_q, k);
           if (lane == 0) atomicMax(&p.sink.tau_g[qi], kth);
           n_q = k;
         }

@@ -14,10 +14,14 @@
 //   warp 2  TMEM allocator / deallocator
 //   warps 4-7  epilogue: thread <-> accumulator lane <-> query row.  tcgen05.ld 32 columns at a time,
 //           3-input max tree, compare with the row's running threshold tau; the common case is one
-//           warp vote and no branch taken.  Survivors are appended to the thread's private candidate
-//           buffer (global memory, L2 resident); a buffer that could overflow is reduced to its exact
-//           top-k by the whole warp (radix select, select.cuh) and tau is raised to the k-th score,
-//           also published to tau_g[query] so every CTA working on the same query benefits.
+//           compare and no branch taken.  Survivors are appended to the thread's private candidate
+//           buffer (global memory); a buffer that could overflow is reduced to its exact top-k by the
+//           whole warp (bitwise-descent select, select.cuh) and tau is raised to the k-th score, also
+//           published to tau_g[query] so every CTA working on the same query benefits.  At the end of a
+//           launch every row appends what it holds to the query's arena slice.
+// A search is several launches of this kernel over a sample-first permutation of the corpus tiles (estimate-only pass,
+// two sample passes, the main pass, a fall-back pass that normally returns at once): DESIGN.md "sampled thresholds";
+// the schedule lives in api.cu, select_tau_kernel / verify_counts_kernel in merge.cu run between the launches.
 // Work decomposition ("interleaved rounds"): the corpus is cut into rounds of R tiles sized to stay
 // L2-resident (tens of MB).  Inside a round the num_qt x R tile-units are laid on a line, query tile major, and cut
 // into P equal pieces, one per cluster -- so every cluster works on the SAME <= 2 query tiles for the whole launch
@@ -45,9 +49,9 @@ template <int CG> struct Cfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (CG == 1) ? 4 : 6;
   static constexpr int RING_BYTES = STAGES * STAGE_BYTES;  // 192 KB either way
-  // ring | full[STAGES] empty[STAGES] tfull[2] tempty[2] | tmem ptr | hist[EPI_WARPS][256]
+  // ring | full[STAGES] empty[STAGES] tfull[2] tempty[2] | tmem ptr
   static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8;
-  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + RING_BYTES + BAR_BYTES + 16 + EPI_WARPS * 256 * 4;
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + RING_BYTES + BAR_BYTES + 16;
 };
 }  // namespace k1
 
@@ -160,7 +164,6 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint64_t* tfull = empty + C::STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_ptr_s = reinterpret_cast<uint32_t*>(tempty + 2);
-  uint32_t* hist = tmem_ptr_s + 4;
 
   if (p.run_flag != nullptr && ld_relaxed_u32(p.run_flag) == 0u) return;  // uniform over the grid: written by an earlier kernel
   const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
@@ -285,7 +288,6 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     // ============================== epilogue ==============================
     const int ew = warp - EPI_WARP0;  // == warp % 4: the TMEM lane quarter this warp may read
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
-    uint32_t* my_hist = hist + ew * 256;
     const int cap = p.sink.cap;
     const int k = p.sink.k;
     const int32_t n_rows = static_cast<int32_t>(p.n);
@@ -383,7 +385,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const int src = __ffs(need) - 1;
             need &= need - 1;
             const int n_src = __shfl_sync(kFullMask, cur.cnt, src);
-            const uint32_t kth = warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
+            const uint32_t kth = warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k);
             if (static_cast<int>(lane) == src) {
               cur.cnt = k;
               cur.tau = fmaxf(cur.tau, okey_inv(kth));
@@ -416,7 +418,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int src = __ffs(big) - 1;
         big &= big - 1;
         const int n_src = __shfl_sync(kFullMask, my_cnt, src);
-        warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k, my_hist);
+        warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k);
         if (static_cast<int>(lane) == src) my_cnt = k;
         __syncwarp();
       }

@@ -224,10 +224,8 @@ static __device__ __noinline__ uint32_t warp_prune_mem(Entry* __restrict__ buf, 
   return kth;
 }
 
-// Dispatcher.  All 32 lanes call with identical arguments; requires n > k >= 1.  (`scratch` is unused: kept so that the
-// kernels' shared-memory layouts do not change.)
-__device__ __forceinline__ uint32_t warp_prune(Entry* __restrict__ buf, int n, int k, uint32_t* scratch) {
-  (void)scratch;
+// Dispatcher.  All 32 lanes call with identical arguments; requires n > k >= 1.
+__device__ __forceinline__ uint32_t warp_prune(Entry* __restrict__ buf, int n, int k) {
   if (n <= 32 * 8) return warp_prune_reg<8>(buf, n, k);
   if (n <= 32 * 16) return warp_prune_reg<16>(buf, n, k);
   if (n <= 32 * 32) return warp_prune_reg<32>(buf, n, k);

@@ -4,8 +4,6 @@
 //   tau_g [nq_pad]              uint32  monotone key of a valid lower bound on each query's final k-th
 //                                       score (atomicMax by every owner after a prune; starts at 0)
 //   qcnt  [nq_pad]              uint32  number of entries flushed to the query's arena slice
-//   lock  [nq_pad]              uint32  K1 only: lock of the query's merged top-k' list (arena slice of k' entries that
-//                                       every finishing owner folds its candidates into; tau_g = its k'-th score)
 //   arena [nq_pad * stride]     Entry   per-query candidate slices, merged by merge_arena_kernel
 //   cand  [owners * cap]        Entry   per-owner private append buffers (owner = epilogue thread in
 //                                       K1, (CTA,row) in KX, (warp,query) in K2)
@@ -18,7 +16,6 @@ namespace nxf {
 struct SinkParams {
   uint32_t* tau_g;
   uint32_t* qcnt;
-  uint32_t* lock;        // per-query spin lock guarding the arena slice (K1's merged-list mode only)
   Entry* arena;
   Entry* cand;
   int64_t arena_stride;  // entries per query in the arena
