@@ -120,6 +120,14 @@ NXF_API const char* nxf_version(void);
 NXF_API const char* nxf_last_error(void);
 /* number of visible CUDA devices (>= 0) or a negative error code */
 NXF_API int nxf_device_count(void);
+/* Host arithmetic only (no device needed): the rank m that nxf_search's sampled thresholds use for a sample of
+ * `sample_tiles` out of `n_tiles` evenly spread corpus tiles and k kept candidates -- the smallest m (capped at k) with
+ * exp(-(m ln(m/lambda) - m + lambda)) <= e^-30, lambda = k * sample_tiles / n_tiles, i.e. a Chernoff bound on
+ * P(Poisson(lambda) >= m), which dominates the hypergeometric count of global top-k rows inside the sample.  The m-th best
+ * score of the sample is then beaten by >= k rows of the whole corpus except with probability < e^-30 per query; results
+ * do not depend on it (counts are verified and a short query is searched again), only speed does.  Replaces nothing in the
+ * reference (Faiss keeps a heap per query); exported so that the bound can be tested without a GPU. */
+NXF_API int nxf_sample_rank(int k, int64_t sample_tiles, int64_t n_tiles);
 
 /* ---- index lifetime ---- */
 /* dim >= 1; metric NXF_METRIC_*; store_dtype NXF_F32/F16/BF16; device = CUDA ordinal.

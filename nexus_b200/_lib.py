@@ -31,7 +31,7 @@ PATH_NONE, PATH_STREAM, PATH_TENSOR, PATH_EXACT, PATH_TSTREAM = 0, 1, 2, 3, 4
 PATH_NAMES = {0: "none", 1: "stream", 2: "tensor", 3: "exact", 4: "tstream"}
 
 EXPORTS = [
-    "nxf_version", "nxf_last_error", "nxf_device_count", "nxf_create", "nxf_destroy", "nxf_reset", "nxf_reserve",
+    "nxf_version", "nxf_last_error", "nxf_device_count", "nxf_sample_rank", "nxf_create", "nxf_destroy", "nxf_reset", "nxf_reserve",
     "nxf_ntotal", "nxf_dim", "nxf_metric", "nxf_store_dtype", "nxf_device", "nxf_set_id_offset", "nxf_get_stats",
     "nxf_set_profiling",
     "nxf_add", "nxf_reconstruct", "nxf_search", "nxf_merge_topk", "nxf_pool_normalize",
@@ -74,6 +74,7 @@ def load() -> C.CDLL:
         lib.nxf_version.restype = C.c_char_p
         lib.nxf_last_error.restype = C.c_char_p
         lib.nxf_device_count.restype = i32
+        lib.nxf_sample_rank.argtypes = [i32, i64, i64]
         lib.nxf_create.argtypes = [i32, i32, i32, i32, C.POINTER(vp)]
         lib.nxf_destroy.argtypes = [vp]
         lib.nxf_destroy.restype = None

@@ -219,6 +219,11 @@ extern "C" {
 const char* nxf_version(void) { return "nexus_flat 0.1.0 (sm_100a; tcgen05/TMA)"; }
 const char* nxf_last_error(void) { return g_err; }
 
+int nxf_sample_rank(int k, int64_t sample_tiles, int64_t n_tiles) {
+  if (k < 1 || sample_tiles < 1 || n_tiles < sample_tiles) return NXF_EINVAL;
+  return std::min(k, sample_rank(k, sample_tiles, n_tiles));
+}
+
 int nxf_device_count(void) {
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);

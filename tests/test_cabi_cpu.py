@@ -87,3 +87,25 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
                 assert "/root/reference" not in src, f
+
+
+@pytest.mark.parametrize("k,s,n", [(128, 135, 34375), (128, 2149, 34375), (1256, 135, 34375), (1256, 2149, 34375), (26, 148, 78125),
+                                   (632, 2516, 78125), (16, 17, 4297), (128, 269, 4297), (2048, 64, 1024), (8, 1, 1024)])
+def test_sample_rank_bounds_the_failure_probability(lib, k, s, n):
+    """nxf_sample_rank (host arithmetic): the number of global top-k rows inside an evenly spread sample of s/n of the corpus is
+    hypergeometric; the search fails to find k candidates above the sample's m-th score only if that count reaches m.  The
+    chosen m keeps that probability below e^-30 (checked with the exact hypergeometric and Poisson tails), is minimal for
+    the Chernoff bound it is derived from, and never exceeds k."""
+    import math
+    from scipy import stats
+    m = lib.nxf_sample_rank(k, s, n)
+    assert 1 <= m <= k
+    lam = k * s / n
+    if m < k:      # m == k is the guaranteed bound (the sample's k-th best), no probability involved
+        chern = lambda mm: mm * math.log(mm / lam) - mm + lam
+        assert chern(m) >= 30.0
+        assert m - 1 <= lam or chern(m - 1) < 30.0
+        assert stats.poisson.logsf(m - 1, lam) <= -30.0
+        rows = 256
+        assert stats.hypergeom.logsf(m - 1, n * rows, k, s * rows) <= -30.0
+    assert lib.nxf_sample_rank(0, s, n) < 0 and lib.nxf_sample_rank(k, n + 1, n) < 0
