@@ -243,6 +243,43 @@ def test_tensor_kernel_sampled_thresholds_fallback():
     run_and_check(c, x, k, store="f32", path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
 
 
+@pytest.mark.parametrize("path,q", [("tensor", 300), ("auto", 40)])
+def test_sampled_thresholds_l2_metric(path, q):
+    """L2 on a corpus long enough for the sample passes (K1 with 300 queries, K2T with 40): the 0.5*|c|^2 adjustment follows the
+    permuted tile order."""
+    rng = np.random.default_rng(12)
+    c = rng.standard_normal((290000, 64)).astype(np.float32)
+    x = rng.standard_normal((q, 64)).astype(np.float32)
+    run_and_check(c, x, 30, store="bf16", path=path, metric="l2", rtol=2e-4, atol=1e-3, min_recall=0.99,
+                  expect_path="tensor" if path == "tensor" else "tstream")
+
+
+def test_tensor_kernel_multi_launch_batches():
+    """More queries than one launch holds (148 SMs: 18 944): full launches and a shorter last one, whose query tiles are shared by more
+    clusters (longer arena slices).  Checked on queries from the first, the middle and the last launch."""
+    from nexus_b200 import FlatIndex
+    n, d, q, k = 270000, 64, 19500, 20
+    c, x = gen_inputs(n, d, q, seed=321)
+    idx = FlatIndex(d, "ip", "bf16")
+    idx.add(c)
+    D, I = idx.search(x, k)
+    assert idx.stats()["last_path_name"] == "tensor"
+    sel = np.r_[0:40, 9000:9040, 18930:18960, 19460:19500]
+    cs = stored(c, "bf16")
+    ref_s, ref_i = oracle.blocked_ip_search(cs, x[sel], k, pad=True)
+    rep = oracle.check_topk(ref_s, ref_i, D[sel], I[sel], cs, x[sel], rtol=1e-5)
+    assert rep.ok, rep.messages[:5]
+    assert (I >= 0).all() and (I < n).all()
+    assert (np.diff(D, axis=1) <= 0).all()
+
+
+@pytest.mark.parametrize("n", [262144 - 256, 262144, 262144 + 1])
+def test_tensor_kernel_at_the_sampling_threshold(n):
+    """n_tiles = 1023 / 1024 / 1025: just below and at the size from which the sample passes run."""
+    c, x = gen_inputs(n, 64, 140, seed=55 + n % 7)
+    run_and_check(c, x, 100, store="bf16", path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
+
+
 def test_tensor_default_dispatch_and_bf16_recall_vs_fp32():
     """BASELINE bar: bf16 recall@k >= 0.999 against the fp32 reference on the same (bf16-valued) corpus."""
     c, x = gen_inputs(50000, 768, 512, seed=77)
