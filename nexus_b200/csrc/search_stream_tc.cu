@@ -21,9 +21,10 @@ namespace k2t {
 constexpr int BLOCK_M = 128;   // corpus rows per tile
 constexpr int BLOCK_K = 64;
 constexpr int UMMA_K = 16;
-constexpr int THREADS = 256;
 constexpr int EPI_WARP0 = 4;
-constexpr int EPI_THREADS = 128;
+constexpr int EPI_SETS = 2;                    // two epilogue warps per SM sub-partition: set s filters tiles s, s + 2, ...
+constexpr int EPI_THREADS = 128 * EPI_SETS;
+constexpr int THREADS = 128 + EPI_THREADS;
 constexpr int TMEM_COLS = 512;
 constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB per stage
 constexpr int MAX_STAGES = 12;
@@ -48,17 +49,18 @@ __device__ __forceinline__ void tmem_ld_wait_dep16(uint32_t (&r)[16]) {
                :
                : "memory");
 }
-// named barrier 1 over the 128 epilogue threads with an OR reduction of a predicate
+// named barrier 1 over the 256 epilogue threads with an OR reduction of a predicate
 __device__ __forceinline__ bool epi_bar_or(bool pred) {
   uint32_t r;
   asm volatile(
       "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\t"
-      "barrier.cta.red.or.pred.aligned q, 1, 128, p;\n\t"
+      "barrier.cta.red.or.pred.aligned q, 1, 256, p;\n\t"
       "selp.u32 %0, 1, 0, q;\n\t}"
       : "=r"(r) : "r"(static_cast<uint32_t>(pred)) : "memory");
   return r != 0;
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("barrier.cta.sync.aligned 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("barrier.cta.sync.aligned 1, 256;" ::: "memory"); }
+static_assert(k2t::EPI_THREADS == 256, "the named barrier above counts 256 threads");
 
 // One 16-query slice of a corpus row's scores: d = v - tau on a max tree; the common case is one compare, branch not taken.
 template <bool L2>
@@ -198,62 +200,69 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     __syncwarp();
   } else if (warp >= EPI_WARP0) {
     // ============================== epilogue ==============================
-    const int ew = warp - EPI_WARP0;
-    const int et = ew * 32 + static_cast<int>(lane);  // 0..127: epilogue thread == corpus row within the tile == query it looks after
+    // Two sets of four warps (one warp of each set per SM sub-partition): set s filters this CTA's tiles s, s + 2, ...  The
+    // thresholds, list counters and lists are shared by both sets (shared-memory atomics); the sets meet every 2*check_every
+    // tiles at a named barrier, where the lists that could overflow are pruned while nobody appends.
+    const int ew8 = warp - EPI_WARP0;  // 0..7
+    const int ew = ew8 & 3;            // == warp % 4: the TMEM lane quarter this warp may read
+    const int set = ew8 >> 2;
+    const int et = ew * 32 + static_cast<int>(lane);   // 0..127: corpus row within the tile
+    const int eq = ew8 * 32 + static_cast<int>(lane);  // 0..255: the query this thread looks after (if < nq)
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
     const int cap = p.sink.cap;
     const int k = p.sink.k;
     Entry* cta_cand = p.sink.cand + static_cast<int64_t>(blockIdx.x) * p.nq_pad * cap;  // [nq_pad][cap]
     uint32_t* cand_words = reinterpret_cast<uint32_t*>(cta_cand);
     const int chunks = p.nq_pad / 16;
-    const int check_every = p.check_every;           // tiles between two overflow checks / threshold refreshes
-    const int full_mark = cap - 2 * check_every * BLOCK_M;  // == 2k': see the margin note below
-    uint32_t iter = 0;
-    int since_check = 0;
-    float tau_next = (et < p.nq) ? tau_load(p.sink.tau_g, et) : INFINITY;
+    const uint32_t round_tiles = 2u * static_cast<uint32_t>(p.check_every);  // tiles between two overflow checks / threshold refreshes
+    // a list gains <= 128 entries per tile, i.e. <= 128 * round_tiles between two checks, and the counts read at a check are
+    // exact (every appender has arrived at the barrier): cap - full_mark = one round of appends
+    const int full_mark = cap - static_cast<int>(round_tiles) * BLOCK_M;
+    const uint32_t n_it = t_first < t_end ? static_cast<uint32_t>((t_end - t_first + gridDim.x - 1) / gridDim.x) : 0u;
+    float tau_next = (eq < p.nq) ? tau_load(p.sink.tau_g, eq) : INFINITY;
 
-    for (int64_t t = t_first; t < t_end; t += gridDim.x, ++iter) {
-      const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
-      const int64_t row = perm_tile(p.perm, t) * BLOCK_M + et;
-      const bool row_ok = row < p.n;
-      const float hn = (L2 && row_ok) ? p.half_norm[row] : 0.f;
-      mbar_wait(&tfull[b], bph);
-      tc_fence_after();
-      const uint32_t tbase = taddr + b * p.tbuf_stride;
-      // two register buffers: the tcgen05.ld of slice ch+1 is in flight while slice ch is filtered
-      uint32_t va[16], vb[16];
-      tmem_ld16(tbase, va);
+    for (uint32_t r0 = 0; r0 < n_it; r0 += round_tiles) {
+      const uint32_t r1 = min(n_it, r0 + round_tiles);
+      for (uint32_t iter = r0 + set; iter < r1; iter += EPI_SETS) {  // r0 is even: the parity of iter is the set
+        const int64_t t = t_first + static_cast<int64_t>(iter) * gridDim.x;
+        const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
+        const int64_t row = perm_tile(p.perm, t) * BLOCK_M + et;
+        const bool row_ok = row < p.n;
+        const float hn = (L2 && row_ok) ? p.half_norm[row] : 0.f;
+        mbar_wait(&tfull[b], bph);
+        tc_fence_after();
+        const uint32_t tbase = taddr + b * p.tbuf_stride;
+        // two register buffers: the tcgen05.ld of slice ch+1 is in flight while slice ch is filtered
+        uint32_t va[16], vb[16];
+        tmem_ld16(tbase, va);
 #pragma unroll 1
-      for (int ch = 0; ch < chunks; ch += 2) {
-        tmem_ld_wait_dep16(va);
-        const bool more = ch + 1 < chunks;
-        if (more) tmem_ld16(tbase + (ch + 1) * 16, vb);
-        else {  // accumulator fully read: hand the buffer back to the MMA issuer
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[b]);
-        }
-        k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
-        if (more) {
-          tmem_ld_wait_dep16(vb);
-          if (ch + 2 < chunks) tmem_ld16(tbase + (ch + 2) * 16, va);
-          else {
+        for (int ch = 0; ch < chunks; ch += 2) {
+          tmem_ld_wait_dep16(va);
+          const bool more = ch + 1 < chunks;
+          if (more) tmem_ld16(tbase + (ch + 1) * 16, vb);
+          else {  // accumulator fully read: hand the buffer back to the MMA issuer
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[b]);
           }
-          k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+          k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+          if (more) {
+            tmem_ld_wait_dep16(vb);
+            if (ch + 2 < chunks) tmem_ld16(tbase + (ch + 2) * 16, va);
+            else {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&tempty[b]);
+            }
+            k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+          }
         }
       }
-      if (p.no_check || ++since_check < check_every) continue;
-      since_check = 0;
-      // ---- every check_every tiles: could any query's buffer overflow before the next check? ----
-      // A query gains <= 128 entries per tile, so <= 128*check_every between checks.  The count read here may miss appends of
-      // warps still inside this interval's last tile, hence a margin of TWO intervals; the barrier orders all appends
-      // before the exact re-read below.
-      const bool any_full = epi_bar_or(et < p.nq && cnt_s[et] > full_mark);
+      if (p.no_check) continue;
+      // ---- end of a round: could any query's list overflow during the next round? ----
+      const bool any_full = epi_bar_or(eq < p.nq && cnt_s[eq] > full_mark);
       if (any_full) {
-        for (int qi = ew; qi < p.nq; qi += 4) {  // warp w prunes queries w, w+4, ...
+        for (int qi = ew8; qi < p.nq; qi += 4 * EPI_SETS) {  // warp w prunes queries w, w+8, ...
           const int n_q = cnt_s[qi];
           if (n_q > full_mark && n_q > k) {
             const uint32_t kth = warp_prune(cta_cand + static_cast<int64_t>(qi) * cap, n_q, k);
@@ -267,10 +276,10 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         }
         epi_bar_sync();
       }
-      // other CTAs' progress: thread et looks after query et (value loaded one interval ago)
-      if (et < p.nq) {
-        if (tau_next > tau_s[et]) tau_s[et] = tau_next;
-        tau_next = tau_load(p.sink.tau_g, et);
+      // other CTAs' progress: thread eq looks after query eq (value loaded one round ago)
+      if (eq < p.nq) {
+        if (tau_next > tau_s[eq]) tau_s[eq] = tau_next;
+        tau_next = tau_load(p.sink.tau_g, eq);
       }
     }
 
@@ -278,9 +287,9 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // list lengths (the lists stay where they are for the seed kernel and the next launch) ----
     epi_bar_sync();
     if (!p.last_pass) {
-      if (et < p.nq) p.cnt_g[static_cast<int64_t>(blockIdx.x) * p.nq_pad + et] = static_cast<uint32_t>(cnt_s[et]);
+      if (eq < p.nq) p.cnt_g[static_cast<int64_t>(blockIdx.x) * p.nq_pad + eq] = static_cast<uint32_t>(cnt_s[eq]);
     } else {
-      for (int qi = ew; qi < p.nq; qi += 4) {
+      for (int qi = ew8; qi < p.nq; qi += 4 * EPI_SETS) {
         int n_q = cnt_s[qi];
         Entry* buf = cta_cand + static_cast<int64_t>(qi) * cap;
         if (n_q > k) {
