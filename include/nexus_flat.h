@@ -179,6 +179,16 @@ NXF_API int nxf_merge_topk(const float* scores, const int64_t* ids, int n_lists,
                            int k_out, int metric, float* out_scores, int64_t* out_ids, int device,
                            void* stream);
 
+/* ---- rank of the positive among the top-k (device pointers only) ----
+ * Replaces torch.cat([pos_scores, topk_scores]) + stable torch.sort(descending) + `indice[:, :k] == 0` in
+ * BaseRetriever.eval_step, Nexus/training/embedder/recommendation/modeling.py:199-205: for every row the positive's
+ * position in the descending stable order of [pos, top_1..top_k] is the number of top-k scores strictly greater than it
+ * (equal scores sort after the positive, which comes first in the concatenation).  pos_scores [nq] float32,
+ * topk_scores [nq, k] float32 (as returned by nxf_search; padding -FLT_MAX counts as a score) ->
+ * rank [nq] int32 in [0, k]  and, if pred is not NULL, pred [nq, k] uint8 with pred[b, j] = (j == rank[b]). */
+NXF_API int nxf_positive_rank(const float* pos_scores, const float* topk_scores, int64_t nq, int k, int32_t* rank,
+                              uint8_t* pred, int device, void* stream);
+
 /* ---- embedder epilogue (device pointers only) ----
  * hidden [B, L, H] of h_dtype (contiguous), mask [B, L] int64 (may be NULL for NXF_POOL_CLS),
  * out [B, H] of out_dtype.  normalize != 0 applies x / max(||x||_2, eps) (F.normalize);

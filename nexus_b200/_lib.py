@@ -34,7 +34,7 @@ EXPORTS = [
     "nxf_version", "nxf_last_error", "nxf_device_count", "nxf_sample_rank", "nxf_create", "nxf_destroy", "nxf_reset", "nxf_reserve",
     "nxf_ntotal", "nxf_dim", "nxf_metric", "nxf_store_dtype", "nxf_device", "nxf_set_id_offset", "nxf_get_stats",
     "nxf_set_profiling",
-    "nxf_add", "nxf_reconstruct", "nxf_search", "nxf_merge_topk", "nxf_pool_normalize",
+    "nxf_add", "nxf_reconstruct", "nxf_search", "nxf_merge_topk", "nxf_positive_rank", "nxf_pool_normalize",
 ]
 
 
@@ -92,6 +92,7 @@ def load() -> C.CDLL:
         lib.nxf_reconstruct.argtypes = [vp, i64, i64, vp, i32, vp]
         lib.nxf_search.argtypes = [vp, vp, i64, i32, i64, i32, i32, vp, vp, i32, i32, vp]
         lib.nxf_merge_topk.argtypes = [vp, vp, i32, i64, i32, i32, i32, vp, vp, i32, vp]
+        lib.nxf_positive_rank.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp]
         lib.nxf_pool_normalize.argtypes = [vp, i32, vp, i64, i64, i64, i32, i32, C.c_float, vp, i32, i32, vp]
         for name in EXPORTS:
             fn = getattr(lib, name)  # raises AttributeError if the symbol is not exported

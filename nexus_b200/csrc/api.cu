@@ -1000,6 +1000,15 @@ int nxf_merge_topk(const float* scores, const int64_t* ids, int n_lists, int64_t
   return launch_merge_lists(p, static_cast<cudaStream_t>(stream_));
 }
 
+int nxf_positive_rank(const float* pos_scores, const float* topk_scores, int64_t nq, int k, int32_t* rank, uint8_t* pred, int device,
+                      void* stream_) {
+  NXF_REQUIRE(pos_scores && topk_scores && rank, "nxf_positive_rank: NULL buffer");
+  NXF_REQUIRE(nq >= 0 && k >= 1, "nxf_positive_rank: bad shape nq=%lld k=%d", (long long)nq, k);
+  DeviceGuard g(device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  return launch_positive_rank(pos_scores, topk_scores, nq, k, rank, pred, static_cast<cudaStream_t>(stream_));
+}
+
 int nxf_pool_normalize(const void* hidden, int h_dtype, const int64_t* mask, int64_t B, int64_t L, int64_t H, int pooling, int normalize,
                        float eps, void* out, int out_dtype, int device, void* stream_) {
   NXF_REQUIRE(hidden != nullptr && out != nullptr, "nxf_pool_normalize: NULL buffer");

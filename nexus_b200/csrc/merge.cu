@@ -517,4 +517,29 @@ int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream) {
   return NXF_OK;
 }
 
+// ---- rank of the positive among the top-k (recsys eval_step) --------------------------------------
+// One warp per row: rank = #{j : topk[j] > pos}; the reference's cat + stable descending sort puts scores equal to the
+// positive after it (modeling.py:199-205).  HBM-bound: nq*k*4 bytes in, nq*(4 + k) out.
+__global__ void __launch_bounds__(256) positive_rank_kernel(const float* __restrict__ pos, const float* __restrict__ topk, int64_t nq, int k,
+                                                            int32_t* __restrict__ rank, uint8_t* __restrict__ pred) {
+  const int64_t b = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5;
+  if (b >= nq) return;  // whole warps
+  const int lane = threadIdx.x & 31;
+  const float p = pos[b];
+  const float* row = topk + b * k;
+  int c = 0;
+  for (int j = lane; j < k; j += 32) c += (row[j] > p) ? 1 : 0;
+  c = __reduce_add_sync(0xFFFFFFFFu, c);
+  if (lane == 0) rank[b] = c;
+  if (pred != nullptr)
+    for (int j = lane; j < k; j += 32) pred[b * k + j] = (j == c) ? 1 : 0;
+}
+
+int launch_positive_rank(const float* pos, const float* topk, int64_t nq, int k, int32_t* rank, uint8_t* pred, cudaStream_t stream) {
+  if (nq <= 0) return NXF_OK;
+  positive_rank_kernel<<<static_cast<unsigned>((nq * 32 + 255) / 256), 256, 0, stream>>>(pos, topk, nq, k, rank, pred);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
 }  // namespace nxf

@@ -257,3 +257,26 @@ def merge_topk(scores, ids, k_out: Optional[int] = None, metric: str = "ip"):
     L.check(L.load().nxf_merge_topk(scores.data_ptr(), ids.data_ptr(), n_lists, nq, k, k_out, _METRICS[metric],
                                     D.data_ptr(), I.data_ptr(), dev, _stream_ptr(dev)))
     return D, I
+
+
+def positive_rank(pos_scores, topk_scores, return_pred: bool = True):
+    """Position of the positive among the top-k, on the device: the fused form of ``torch.cat([pos, topk])`` + stable
+    descending ``torch.sort`` + ``indice[:, :k] == 0`` in ``BaseRetriever.eval_step``
+    (Nexus/training/embedder/recommendation/modeling.py:199-205).
+
+    ``pos_scores`` [B] or [B, 1] and ``topk_scores`` [B, k] CUDA tensors -> ``rank`` int32 [B] in [0, k] (k = the positive
+    is behind all k) and, with ``return_pred``, ``pred`` bool [B, k] exactly as the reference's ``pred``."""
+    torch = _torch()
+    if not (pos_scores.is_cuda and topk_scores.is_cuda):
+        raise ValueError("positive_rank works on CUDA tensors only (there is no CPU path)")
+    topk = topk_scores.contiguous().float()
+    pos = pos_scores.reshape(-1).contiguous().float()
+    B, k = topk.shape
+    if pos.shape[0] != B:
+        raise ValueError(f"pos_scores has {pos.shape[0]} rows, topk_scores {B}")
+    rank = torch.empty((B,), dtype=torch.int32, device=topk.device)
+    pred = torch.empty((B, k), dtype=torch.uint8, device=topk.device) if return_pred else None
+    dev = topk.device.index
+    L.check(L.load().nxf_positive_rank(pos.data_ptr(), topk.data_ptr(), B, k, rank.data_ptr(),
+                                       pred.data_ptr() if return_pred else 0, dev, _stream_ptr(dev)))
+    return (rank, pred.bool()) if return_pred else rank

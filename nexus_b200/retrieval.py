@@ -89,3 +89,31 @@ def search(faiss_index: Any, k: int = 100, query_embeddings: Optional[np.ndarray
         all_scores.append(s)
         all_indices.append(ix)
     return np.concatenate(all_scores, axis=0), np.concatenate(all_indices, axis=0)
+
+
+def unpack_results(queries_ids, corpus_ids, all_scores, all_indices, ignore_identical_ids: bool = False):
+    """``{query_id: {doc_id: float(score)}}`` from the ``[Q, k]`` arrays, identical to the nested loop at
+    Nexus/evaluation/text_retrieval/searcher.py:152-159 (``-1`` ids skipped; with ``ignore_identical_ids`` a document whose
+    id equals the query's is dropped) but without Q*k Python-level iterations: the arrays are converted once
+    (``tolist``), ids are looked up per row with list indexing, and rows without padding take a dict(zip()) fast path.
+    Later duplicates of a document id overwrite earlier ones, as in the reference."""
+    scores = np.asarray(all_scores)
+    indices = np.asarray(all_indices)
+    if scores.shape != indices.shape or scores.ndim != 2:
+        raise ValueError(f"scores {scores.shape} and indices {indices.shape} must be the same [Q, k] shape")
+    if len(queries_ids) != scores.shape[0]:
+        raise ValueError(f"{len(queries_ids)} query ids for {scores.shape[0]} result rows")
+    corpus_ids = corpus_ids if isinstance(corpus_ids, list) else list(corpus_ids)
+    has_pad = (indices < 0).any(axis=1).tolist()
+    s_rows = scores.astype(np.float64).tolist()       # float(np.float32) == the float64 value of the float32
+    i_rows = indices.tolist()
+    results = {}
+    for qid, srow, irow, pad in zip(queries_ids, s_rows, i_rows, has_pad):
+        if pad:
+            pairs = [(corpus_ids[i], s) for i, s in zip(irow, srow) if i != -1]
+        else:
+            pairs = list(zip([corpus_ids[i] for i in irow], srow))
+        if ignore_identical_ids:
+            pairs = [(d, s) for d, s in pairs if d != qid]
+        results[qid] = dict(pairs)
+    return results

@@ -39,3 +39,4 @@ from .pooling import (  # noqa: F401
     l2_normalize_numpy,
     pool_and_normalize,
 )
+from .callers import unpack_results_loop, positive_pred  # noqa: F401

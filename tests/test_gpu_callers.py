@@ -1,0 +1,57 @@
+"""GPU parity of the callers right after the search: rank of the positive among the top-k, through the
+C ABI (nxf_positive_rank), against the oracle's restatement of modeling.py:199-205.  Bit-exact (integer / boolean)."""
+import numpy as np
+import pytest
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("B,k", [(1, 1), (5, 7), (64, 10), (333, 100), (4096, 50), (17, 1000)])
+def test_positive_rank_matches_reference_sort(B, k):
+    import torch
+    from nexus_b200 import positive_rank
+    rng = np.random.default_rng(B * 31 + k)
+    topk = np.sort(rng.standard_normal((B, k)).astype(np.float32), axis=1)[:, ::-1].copy()
+    pos = rng.standard_normal(B).astype(np.float32)
+    for b in range(0, B, 3):                       # ties with a top-k score
+        pos[b] = topk[b, rng.integers(0, k)]
+    if B > 2:
+        pos[1] = topk[1].max() + 1                 # rank 0
+        pos[2] = topk[2].min() - 1                 # behind all k
+    rank, pred = positive_rank(torch.from_numpy(pos).cuda(), torch.from_numpy(topk).cuda())
+    ref_rank, ref_pred = oracle.positive_pred(pos, topk)
+    np.testing.assert_array_equal(rank.cpu().numpy(), ref_rank)
+    np.testing.assert_array_equal(pred.cpu().numpy(), ref_pred)
+    only = positive_rank(torch.from_numpy(pos).cuda().unsqueeze(-1), torch.from_numpy(topk).cuda(), return_pred=False)
+    np.testing.assert_array_equal(only.cpu().numpy(), ref_rank)
+
+
+def test_positive_rank_after_a_search():
+    """eval_step end to end: search the item table, score the positive, rank it (modeling.py:190-205)."""
+    import torch
+    from nexus_b200 import FlatIndex, positive_rank
+    gen = torch.Generator().manual_seed(5)
+    items = torch.randn(20000, 64, generator=gen)
+    q = torch.randn(256, 64, generator=gen)
+    target = torch.randint(0, items.shape[0], (256,), generator=gen)
+    q = q + 2.0 * items[target]                    # the positive scores high for most rows
+    index = FlatIndex(64, "ip", store_dtype="f32", device=0)
+    index.add(items.numpy())
+    scores, ids = index.search(q.numpy(), 20)
+    pos = (q * items[target]).sum(-1)
+    rank, pred = positive_rank(pos.cuda(), torch.from_numpy(scores).cuda())
+    ref_rank, ref_pred = oracle.positive_pred(pos.numpy(), scores)
+    np.testing.assert_array_equal(rank.cpu().numpy(), ref_rank)
+    np.testing.assert_array_equal(pred.cpu().numpy(), ref_pred)
+    assert (ref_rank < 20).mean() > 0.5
+
+
+def test_positive_rank_errors_are_loud():
+    import torch
+    from nexus_b200 import positive_rank
+    with pytest.raises(ValueError):
+        positive_rank(torch.zeros(3), torch.zeros(3, 4))
+    with pytest.raises(ValueError):
+        positive_rank(torch.zeros(2).cuda(), torch.zeros(3, 4).cuda())
