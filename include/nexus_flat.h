@@ -99,7 +99,7 @@ enum {
 #define NXF_MAX_K 2048
 
 /* which kernel family served the last search on this handle (nxf_stats.last_path) */
-enum { NXF_PATH_NONE = 0, NXF_PATH_STREAM = 1, NXF_PATH_TENSOR = 2, NXF_PATH_EXACT = 3, NXF_PATH_TSTREAM = 4 };
+enum { NXF_PATH_NONE = 0, NXF_PATH_STREAM = 1, NXF_PATH_TENSOR = 2, NXF_PATH_EXACT = 3, NXF_PATH_TSTREAM = 4, NXF_PATH_SUBSET = 5 };
 
 typedef struct nxf_stats {
   int64_t kernel_launches; /* number of this library's kernels launched on behalf of the handle */
@@ -169,6 +169,22 @@ NXF_API int nxf_reconstruct(nxf_index* idx, int64_t first, int64_t n, float* dst
 NXF_API int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld,
                        int q_on_device, int k, float* out_scores, int64_t* out_ids, int out_on_device,
                        int flags, void* stream);
+
+/* ---- per-query candidate lists ("local ranking") ----
+ * Replaces the loop at Nexus/evaluation/mmeb_v2/eval_embedding.py:384-404 (eval_type != "global"): per query, stack the
+ * embeddings of that query's own candidates, q @ cand^T (models.py:186-188), torch.sort(descending); the metrics read the
+ * first 10 entries (utils/eval_utils/metrics.py:12).  The candidate embeddings are rows of the index; query i ranks the rows
+ * rows[offsets[i] .. offsets[i+1]) (CSR; a row may appear in many lists and more than once in one list).
+ * out_scores [nq,k] float32 and out_pos [nq,k] int64: the POSITIONS inside the query's own list (what the reference's
+ * `ranked_idx` holds), best first, ties by ascending position (the order of a stable descending sort); columns beyond the
+ * list length are padded with -1 and -FLT_MAX (IP) / +FLT_MAX (L2).  Scores are fp32 arithmetic on the stored rows and the
+ * fp32 queries (inner product, or squared L2 distance for an L2 index).
+ * q, (offsets, rows) and the outputs are host or device pointers as the three *_on_device flags say; total = offsets[nq].
+ * A row id outside [0, ntotal) or a malformed offsets array is an error (NXF_EINVAL; the reference raises KeyError on an
+ * unknown candidate name): the call synchronises `stream` to report it. */
+NXF_API int nxf_search_subsets(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device,
+                               const int64_t* offsets, const int64_t* rows, int64_t total, int lists_on_device, int k,
+                               float* out_scores, int64_t* out_pos, int out_on_device, void* stream);
 
 /* ---- multi-shard merge (device pointers only) ----
  * scores [n_lists, nq, k] float32 and ids [n_lists, nq, k] int64 (global ids, -1 = padding), each

@@ -27,14 +27,14 @@ SEARCH_TENSOR_1CTA = 1 << 4
 SEARCH_FORCE_TSTREAM = 1 << 5
 STREAM_MAX_NQ = 4
 MAX_K = 2048
-PATH_NONE, PATH_STREAM, PATH_TENSOR, PATH_EXACT, PATH_TSTREAM = 0, 1, 2, 3, 4
-PATH_NAMES = {0: "none", 1: "stream", 2: "tensor", 3: "exact", 4: "tstream"}
+PATH_NONE, PATH_STREAM, PATH_TENSOR, PATH_EXACT, PATH_TSTREAM, PATH_SUBSET = 0, 1, 2, 3, 4, 5
+PATH_NAMES = {0: "none", 1: "stream", 2: "tensor", 3: "exact", 4: "tstream", 5: "subset"}
 
 EXPORTS = [
     "nxf_version", "nxf_last_error", "nxf_device_count", "nxf_sample_rank", "nxf_create", "nxf_destroy", "nxf_reset", "nxf_reserve",
     "nxf_ntotal", "nxf_dim", "nxf_metric", "nxf_store_dtype", "nxf_device", "nxf_set_id_offset", "nxf_get_stats",
     "nxf_set_profiling",
-    "nxf_add", "nxf_reconstruct", "nxf_search", "nxf_merge_topk", "nxf_positive_rank", "nxf_pool_normalize",
+    "nxf_add", "nxf_reconstruct", "nxf_search", "nxf_search_subsets", "nxf_merge_topk", "nxf_positive_rank", "nxf_pool_normalize",
 ]
 
 
@@ -91,6 +91,7 @@ def load() -> C.CDLL:
         lib.nxf_add.argtypes = [vp, vp, i64, i32, i64, i32, vp]
         lib.nxf_reconstruct.argtypes = [vp, i64, i64, vp, i32, vp]
         lib.nxf_search.argtypes = [vp, vp, i64, i32, i64, i32, i32, vp, vp, i32, i32, vp]
+        lib.nxf_search_subsets.argtypes = [vp, vp, i64, i32, i64, i32, vp, vp, i64, i32, i32, vp, vp, i32, vp]
         lib.nxf_merge_topk.argtypes = [vp, vp, i32, i64, i32, i32, i32, vp, vp, i32, vp]
         lib.nxf_positive_rank.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp]
         lib.nxf_pool_normalize.argtypes = [vp, i32, vp, i64, i64, i64, i32, i32, C.c_float, vp, i32, i32, vp]

@@ -19,8 +19,8 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 LIB = os.path.join(HERE, "libnexus_flat.so")
 OBJ_DIR = os.path.join(HERE, "_build")
 
-SOURCES = ["api.cu", "convert.cu", "merge.cu", "pool.cu", "search_exact.cu", "search_stream.cu", "search_stream_tc.cu", "search_tc.cu"]
-HEADERS = ["common.cuh", "select.cuh", "sink.cuh", "params.cuh"]
+SOURCES = ["api.cu", "convert.cu", "merge.cu", "pool.cu", "search_exact.cu", "search_stream.cu", "search_stream_tc.cu", "search_subset.cu", "search_tc.cu"]
+HEADERS = ["common.cuh", "select.cuh", "sink.cuh", "params.cuh", "block_sort.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -982,6 +982,105 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
 }
 
 // ------------------------------------------------------------------------------------------
+// per-query candidate lists (KS, search_subset.cu)
+// ------------------------------------------------------------------------------------------
+int nxf_search_subsets(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, const int64_t* offsets,
+                       const int64_t* rows, int64_t total, int lists_on_device, int k, float* out_scores, int64_t* out_pos,
+                       int out_on_device, void* stream_) {
+  NXF_REQUIRE(idx != nullptr, "nxf_search_subsets: NULL index");
+  NXF_REQUIRE(nq >= 0 && total >= 0, "nxf_search_subsets: negative count (nq=%lld total=%lld)", (long long)nq, (long long)total);
+  NXF_REQUIRE(nq < (int64_t(1) << 31), "nxf_search_subsets: nq=%lld too large for one call", (long long)nq);
+  NXF_REQUIRE(k >= 1 && k <= NXF_MAX_K, "nxf_search_subsets: k=%d outside [1, %d]", k, NXF_MAX_K);
+  if (nq == 0) return NXF_OK;
+  NXF_REQUIRE(q != nullptr && offsets != nullptr && out_scores != nullptr && out_pos != nullptr, "nxf_search_subsets: NULL buffer");
+  NXF_REQUIRE(rows != nullptr || total == 0, "nxf_search_subsets: NULL row list");
+  int rc = check_dtype(q_dtype, "nxf_search_subsets(q_dtype)");
+  if (rc) return rc;
+  if (q_ld == 0) q_ld = idx->dim;
+  NXF_REQUIRE(q_ld >= idx->dim, "nxf_search_subsets: query stride %lld smaller than dim %d", (long long)q_ld, idx->dim);
+  if (!lists_on_device) {
+    NXF_REQUIRE(offsets[0] == 0 && offsets[nq] == total, "nxf_search_subsets: offsets must run from 0 to total=%lld (got %lld..%lld)",
+                (long long)total, (long long)offsets[0], (long long)offsets[nq]);
+  }
+
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const size_t qsz = dtype_size(q_dtype);
+
+  unsigned char* base = nullptr;
+  unsigned char* q_src = nullptr; float* q_f32 = nullptr; int64_t* d_off = nullptr; int64_t* d_rows = nullptr; Entry* scr = nullptr;
+  float* o_scores = nullptr; int64_t* o_pos = nullptr; uint32_t* err = nullptr;
+  for (int pass = 0; pass < 2; ++pass) {
+    Carver cv(base);
+    err = cv.take<uint32_t>(64);
+    q_src = q_on_device ? nullptr : cv.take<unsigned char>(static_cast<size_t>(nq) * q_ld * qsz);
+    q_f32 = cv.take<float>(static_cast<size_t>(nq) * idx->ld);
+    if (!lists_on_device) {
+      d_off = cv.take<int64_t>(static_cast<size_t>(nq) + 1);
+      d_rows = cv.take<int64_t>(static_cast<size_t>(std::max<int64_t>(total, 1)));
+    }
+    scr = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(total, 1)));
+    if (!out_on_device) {
+      o_scores = cv.take<float>(static_cast<size_t>(nq) * k);
+      o_pos = cv.take<int64_t>(static_cast<size_t>(nq) * k);
+    }
+    if (pass == 0) {
+      rc = ensure_scratch(idx, cv.off + 256);
+      if (rc) return rc;
+      base = idx->scratch;
+    }
+  }
+  NXF_CUDA(cudaMemsetAsync(err, 0, sizeof(uint32_t), stream));
+  const void* q_dev = q;
+  if (!q_on_device) {
+    NXF_CUDA(cudaMemcpyAsync(q_src, q, static_cast<size_t>(nq) * q_ld * qsz, cudaMemcpyHostToDevice, stream));
+    q_dev = q_src;
+  }
+  if (!lists_on_device) {
+    NXF_CUDA(cudaMemcpyAsync(d_off, offsets, (static_cast<size_t>(nq) + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+    if (total > 0) NXF_CUDA(cudaMemcpyAsync(d_rows, rows, static_cast<size_t>(total) * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+  }
+  rc = launch_convert_rows(q_dev, q_dtype, q_ld, q_f32, NXF_F32, idx->ld, nq, idx->dim, stream);
+  if (rc) return rc;
+  idx->stats.kernel_launches++;
+
+  SubsetParams sp;
+  sp.q = q_f32; sp.ldq = idx->ld; sp.corpus = idx->data; sp.ld = idx->ld; sp.dim = idx->dim; sp.n_rows = idx->n;
+  sp.offsets = lists_on_device ? offsets : d_off; sp.rows = lists_on_device ? rows : d_rows; sp.total = total; sp.scratch = scr;
+  sp.k_out = k; sp.metric = idx->metric;
+  sp.out_scores = out_on_device ? out_scores : o_scores; sp.out_pos = out_on_device ? out_pos : o_pos; sp.err = err;
+  cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+  if (idx->profiling) {
+    NXF_CUDA(cudaEventCreate(&pe0));
+    NXF_CUDA(cudaEventCreate(&pe1));
+    NXF_CUDA(cudaEventRecord(pe0, stream));
+  }
+  rc = launch_subset_search(idx->store_dtype, sp, nq, stream);
+  if (rc) return rc;
+  idx->stats.kernel_launches++;
+  if (pe0) {
+    NXF_CUDA(cudaEventRecord(pe1, stream));
+    idx->prof_events.emplace_back(pe0, pe1);
+  }
+  if (!out_on_device) {
+    NXF_CUDA(cudaMemcpyAsync(out_scores, o_scores, static_cast<size_t>(nq) * k * sizeof(float), cudaMemcpyDeviceToHost, stream));
+    NXF_CUDA(cudaMemcpyAsync(out_pos, o_pos, static_cast<size_t>(nq) * k * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+  }
+  uint32_t h_err = 0;
+  NXF_CUDA(cudaMemcpyAsync(&h_err, err, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  NXF_CUDA(cudaStreamSynchronize(stream));
+  idx->stats.searches++;
+  idx->stats.last_path = NXF_PATH_SUBSET;
+  idx->stats.last_k_fetch = k;
+  idx->stats.last_grid = static_cast<int32_t>(std::min<int64_t>(nq, INT32_MAX));
+  NXF_REQUIRE(!(h_err & 2u), "nxf_search_subsets: offsets are not a non-decreasing CSR inside [0, total=%lld]", (long long)total);
+  NXF_REQUIRE(!(h_err & 1u), "nxf_search_subsets: a candidate row id lies outside [0, ntotal=%lld)", (long long)idx->n);
+  return NXF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // merge + pool (device pointers only)
 // ------------------------------------------------------------------------------------------
 int nxf_merge_topk(const float* scores, const int64_t* ids, int n_lists, int64_t nq, int k, int k_out, int metric, float* out_scores,

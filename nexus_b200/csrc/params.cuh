@@ -122,6 +122,24 @@ struct MergeArenaParams {
   int64_t* out_ids;   // [nq, k_out]
 };
 
+struct SubsetParams {
+  const float* q;          // [nq, ldq] fp32, device
+  int64_t ldq;
+  const void* corpus;      // [n_rows, ld] of the storage type
+  int64_t ld;
+  int dim;
+  int64_t n_rows;
+  const int64_t* offsets;  // [nq + 1] CSR offsets into rows
+  const int64_t* rows;     // [total] index rows of every query's candidates
+  int64_t total;
+  Entry* scratch;          // [total] (score, position) of lists longer than NXF_MAX_K
+  int k_out;
+  int metric;
+  float* out_scores;       // [nq, k_out]
+  int64_t* out_pos;        // [nq, k_out] positions inside the query's own list, -1 = padding
+  uint32_t* err;           // bit 0: a row id outside [0, n_rows); bit 1: malformed offsets
+};
+
 struct MergeListsParams {
   const float* scores;  // [n_lists, nq, k]
   const int64_t* ids;   // [n_lists, nq, k]
@@ -150,6 +168,7 @@ int launch_select_tau(Entry* arena, uint32_t* qcnt, int64_t arena_stride, int m,
 int launch_verify_counts(uint32_t* qcnt, uint32_t* tau_g, int64_t nq, int need, uint32_t* flag, cudaStream_t stream);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
+int launch_subset_search(int store_dtype, const SubsetParams& p, int64_t nq, cudaStream_t stream);
 int launch_positive_rank(const float* pos, const float* topk, int64_t nq, int k, int32_t* rank, uint8_t* pred, cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,
                         cudaStream_t stream);

@@ -228,6 +228,49 @@ class FlatIndex:
         L.check(self._lib.nxf_search(self._h, b.ptr, b.n, b.dtype, b.ld, 0, k, D.ctypes.data, I.ctypes.data, 0, flags, stream))
         return D, I
 
+    def search_subsets(self, x, offsets, rows, k: int) -> Tuple:
+        """Per-query candidate lists: query ``i`` ranks the index rows ``rows[offsets[i]:offsets[i+1]]`` (CSR) and gets the
+        best ``k`` POSITIONS inside its own list -> ``(D float32 [n,k], P int64 [n,k])``, best first, ties by ascending position,
+        ``-1`` padding beyond the list length.  The device form of the local-ranking loop at
+        Nexus/evaluation/mmeb_v2/eval_embedding.py:384-404.  ``offsets``/``rows`` int64, both numpy/CPU or both CUDA tensors."""
+        b = _as_rows(x, self.d, "search_subsets")
+        k = int(k)
+        stream = _stream_ptr(self._device)
+        lists_on_device = _is_tensor(offsets) and offsets.is_cuda
+        if lists_on_device != (_is_tensor(rows) and rows.is_cuda):
+            raise ValueError("search_subsets: offsets and rows must both be CUDA tensors or both host arrays")
+        if lists_on_device:
+            torch = _torch()
+            if offsets.device.index != self._device or rows.device.index != self._device:
+                raise ValueError(f"search_subsets: the lists must live on cuda:{self._device}")
+            off = offsets.to(torch.int64).contiguous()
+            rws = rows.to(torch.int64).contiguous()
+            if off.dim() != 1 or off.numel() != b.n + 1:
+                raise ValueError(f"search_subsets: offsets has {off.numel()} entries for {b.n} queries (want nq + 1)")
+            total, off_ptr, rows_ptr = int(rws.numel()), off.data_ptr(), rws.data_ptr()
+        else:
+            off = np.ascontiguousarray(np.asarray(offsets.cpu() if _is_tensor(offsets) else offsets, dtype=np.int64))
+            rws = np.ascontiguousarray(np.asarray(rows.cpu() if _is_tensor(rows) else rows, dtype=np.int64))
+            if off.ndim != 1 or off.size != b.n + 1:
+                raise ValueError(f"search_subsets: offsets has {off.size} entries for {b.n} queries (want nq + 1)")
+            total, off_ptr, rows_ptr = int(rws.size), off.ctypes.data, rws.ctypes.data
+        call = self._lib.nxf_search_subsets
+        if b.kind == "torch":
+            torch = _torch()
+            if b.on_device and b.device != self._device:
+                raise ValueError(f"search_subsets: queries live on cuda:{b.device}, index on cuda:{self._device}")
+            dev = b.keep.device if b.on_device else "cpu"
+            D = torch.empty((b.n, k), dtype=torch.float32, device=dev)
+            P = torch.empty((b.n, k), dtype=torch.int64, device=dev)
+            L.check(call(self._h, b.ptr, b.n, b.dtype, b.ld, b.on_device, off_ptr, rows_ptr, total, int(lists_on_device), k,
+                         D.data_ptr(), P.data_ptr(), b.on_device, stream))
+            return D, P
+        D = np.empty((b.n, k), dtype=np.float32)
+        P = np.empty((b.n, k), dtype=np.int64)
+        L.check(call(self._h, b.ptr, b.n, b.dtype, b.ld, 0, off_ptr, rows_ptr, total, int(lists_on_device), k,
+                     D.ctypes.data, P.ctypes.data, 0, stream))
+        return D, P
+
     def set_profiling(self, enable: bool = True) -> None:
         """Time every main search kernel with CUDA events on its stream (read back through stats())."""
         L.check(self._lib.nxf_set_profiling(self._h, 1 if enable else 0))

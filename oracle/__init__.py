@@ -39,4 +39,11 @@ from .pooling import (  # noqa: F401
     l2_normalize_numpy,
     pool_and_normalize,
 )
-from .callers import unpack_results_loop, positive_pred  # noqa: F401
+from .callers import (  # noqa: F401
+    unpack_results_loop,
+    positive_pred,
+    mmeb_similarity,
+    mmeb_global_ranking,
+    mmeb_local_ranking,
+    mmeb_pred_dicts,
+)
