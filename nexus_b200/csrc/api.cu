@@ -7,6 +7,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "params.cuh"
@@ -188,6 +189,21 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // K1's arena slice of a query: the list left by the sample passes (<= k' entries) + up to k' entries from every cluster that owns a
 // piece of the query's tile in the last pass (a tile's line segment is cut by pieces of num_qt / clusters of its length)
+// Host rows -> pinned staging with several threads: one thread copies at 8-12 GB/s, a Gen5 x16 link moves ~55 GB/s, so the
+// add of a host corpus (utils.py:169,189: N*D*4 bytes) is bound by this copy unless it is split (NXF_ADD_THREADS, default 8).
+void parallel_memcpy(unsigned char* dst, const unsigned char* src, size_t bytes, int threads) {
+  if (threads <= 1 || bytes < (size_t(8) << 20)) { std::memcpy(dst, src, bytes); return; }
+  const size_t part = (bytes / threads + 4095) & ~size_t(4095);
+  std::vector<std::thread> th;
+  for (int t = 1; t < threads; ++t) {
+    const size_t o = static_cast<size_t>(t) * part;
+    if (o >= bytes) break;
+    th.emplace_back([=] { std::memcpy(dst + o, src + o, std::min(part, bytes - o)); });
+  }
+  std::memcpy(dst, src, std::min(part, bytes));
+  for (auto& x : th) x.join();
+}
+
 int64_t k1_arena_stride(int64_t clusters, int64_t num_qt, int k_fetch) {
   const int64_t owners_max = std::min<int64_t>(clusters, (clusters + num_qt - 1) / std::max<int64_t>(num_qt, 1) + 1);
   return (owners_max + 1) * k_fetch;
@@ -383,10 +399,11 @@ int nxf_add(nxf_index* idx, const void* rows, int64_t n, int src_dtype, int64_t 
     const unsigned char* src = static_cast<const unsigned char*>(rows);
     int b = 0;
     bool used[2] = {false, false};
+    const int add_threads = std::max(1, std::min(env_int("NXF_ADD_THREADS", 8), static_cast<int>(std::thread::hardware_concurrency())));
     for (int64_t r0 = 0; r0 < n; r0 += static_cast<int64_t>(chunk_rows), b ^= 1) {
       const int64_t rn = std::min<int64_t>(static_cast<int64_t>(chunk_rows), n - r0);
       if (used[b]) NXF_CUDA(cudaEventSynchronize(ev[b]));  // staging buffer b free again
-      std::memcpy(idx->pinned + b * chunk_bytes, src + static_cast<size_t>(r0) * row_bytes, static_cast<size_t>(rn) * row_bytes);
+      parallel_memcpy(idx->pinned + b * chunk_bytes, src + static_cast<size_t>(r0) * row_bytes, static_cast<size_t>(rn) * row_bytes, add_threads);
       NXF_CUDA(cudaMemcpyAsync(idx->scratch + b * chunk_bytes, idx->pinned + b * chunk_bytes, static_cast<size_t>(rn) * row_bytes,
                                cudaMemcpyHostToDevice, stream));
       rc = launch_convert_rows(idx->scratch + b * chunk_bytes, src_dtype, src_ld, dst + static_cast<size_t>(r0) * idx->ld * esz,
@@ -832,6 +849,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
           bounds[++n_pass] = kp.perm.ns;
         }
       }
+      kp.perm.finish();
       bounds[++n_pass] = P.n_tiles;
       for (int ps = 0; ps + 1 < n_pass; ++ps) {
         kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
@@ -902,6 +920,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
         if (est) {
           kp.perm.s = s1; kp.perm.ns = ceil_div64(P.n_tiles, s1);
           kp.perm.s0 = s0; kp.perm.n0 = ceil_div64(kp.perm.ns, s0);
+          kp.perm.finish();
           // estimate-only pass: a few tiles per cluster (so that no row fills its buffer), only slice maxima are recorded; it spares
           // the first sample pass the cost of starting from -inf (every score appended, every row pruned after its first tile)
           const int64_t clusters = grid / P.cta_group;

@@ -26,21 +26,33 @@ struct KxParams {
 // tiles 0, s, 2s, ... -- of those, every s0-th comes first (n0 tiles) -- then all the others in order.  s <= 1: identity.
 struct TilePerm {
   int64_t s = 0, ns = 0, s0 = 0, n0 = 0;
+  // floor(2^64 / d) + 1 for d = s - 1 and d = s0 - 1 (0 when d <= 1): j / d == hi64(j * m) exactly for every 32-bit j, which keeps
+  // the per-tile index arithmetic of the single producer / issuer threads off the integer-division slow path
+  uint64_t m1 = 0, m0 = 0;
+  void finish() {
+    m1 = s - 1 > 1 ? ~uint64_t(0) / static_cast<uint64_t>(s - 1) + 1 : 0;
+    m0 = s0 - 1 > 1 ? ~uint64_t(0) / static_cast<uint64_t>(s0 - 1) + 1 : 0;
+  }
 };
 #ifdef __CUDACC__
+__device__ __forceinline__ uint32_t perm_div(uint32_t j, uint64_t m) {  // j / d with m = floor(2^64 / d) + 1; m == 0: d == 1
+  if (m == 0) return j;
+  const uint64_t t = static_cast<uint64_t>(j) * static_cast<uint32_t>(m >> 32) + __umulhi(j, static_cast<uint32_t>(m));
+  return static_cast<uint32_t>(t >> 32);
+}
 __device__ __forceinline__ int64_t perm_tile(const TilePerm& tp, int64_t v64) {
   if (tp.s <= 1) return v64;
-  // tile indices fit 32 bits (< 2^31 rows per device): 32-bit divisions
-  const uint32_t v = static_cast<uint32_t>(v64), s = static_cast<uint32_t>(tp.s), ns = static_cast<uint32_t>(tp.ns);
+  // tile indices fit 32 bits (< 2^31 rows per device)
+  const uint32_t v = static_cast<uint32_t>(v64), ns = static_cast<uint32_t>(tp.ns);
   if (v >= ns) {  // the j-th tile that is not a multiple of s
     const uint32_t j = v - ns;
-    return static_cast<int64_t>(j + j / (s - 1u) + 1u);
+    return static_cast<int64_t>(j + perm_div(j, tp.m1) + 1u);
   }
   uint32_t i = v;  // index among the multiples of s
   if (tp.s0 > 1) {
     const uint32_t s0 = static_cast<uint32_t>(tp.s0), n0 = static_cast<uint32_t>(tp.n0);
     if (v < n0) i = v * s0;
-    else { const uint32_t j = v - n0; i = j + j / (s0 - 1u) + 1u; }
+    else { const uint32_t j = v - n0; i = j + perm_div(j, tp.m0) + 1u; }
   }
   return static_cast<int64_t>(i) * tp.s;
 }

@@ -168,26 +168,30 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       const uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M, p.nq_pad);
       mbar_wait(qfull, 0);
       tc_fence_after();
+      // This single thread paces the whole stream on short rows (one K block per tile: a tile every ~700 clocks at HBM speed), so
+      // its per-tile instruction chain is kept short: running counters instead of divisions, descriptors advanced by addition.
       int s = 0;
       uint32_t ph = 0;
-      uint32_t iter = 0;
-      for (int64_t t = t_first; t < t_end; t += gridDim.x, ++iter) {
-        const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
+      uint32_t b = 0, bph = 0;
+      const uint64_t a_desc0 = umma_desc_sw128(smem_u32(ring));          // stage s: + s * (A_BYTES >> 4) in the address field
+      const uint64_t b_desc0 = umma_desc_sw128(smem_u32(q_smem));        // query block qb: + qb * (nq_pad * 128 >> 4)
+      const uint32_t q_blk = static_cast<uint32_t>(p.nq_pad) * 8u;
+      for (int64_t t = t_first; t < t_end; t += gridDim.x) {
         mbar_wait(&tempty[b], bph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + b * p.tbuf_stride;
         for (int kb = 0; kb < p.kblocks; ++kb) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
-          const uint64_t a_desc = umma_desc_sw128(smem_u32(ring + s * A_BYTES));
+          const uint64_t a_desc = a_desc0 + static_cast<uint32_t>(s) * static_cast<uint32_t>(A_BYTES >> 4);
           // split storage: corpus block kb of the hi plane meets q_hi[kb] and q_mid[kb]; of the mid plane, q_hi[kb - split_kb]
           const int qb = (p.split_kb > 0 && kb >= p.split_kb) ? kb - p.split_kb : kb;
-          const uint64_t b_desc = umma_desc_sw128(smem_u32(q_smem + qb * p.nq_pad * 128));
+          const uint64_t b_desc = b_desc0 + static_cast<uint32_t>(qb) * q_blk;
+          umma_f16<1>(d_tmem, a_desc, b_desc, idesc, kb != 0 ? 1u : 0u);
 #pragma unroll
-          for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4)
-            umma_f16<1>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, (kb | k4) != 0 ? 1u : 0u);
+          for (int k4 = 1; k4 < BLOCK_K / UMMA_K; ++k4) umma_f16<1>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, 1u);
           if (p.split_kb > 0 && kb < p.split_kb) {
-            const uint64_t b2_desc = umma_desc_sw128(smem_u32(q_smem + (kb + p.split_kb) * p.nq_pad * 128));
+            const uint64_t b2_desc = b_desc0 + static_cast<uint32_t>(kb + p.split_kb) * q_blk;
 #pragma unroll
             for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) umma_f16<1>(d_tmem, a_desc + 2 * k4, b2_desc + 2 * k4, idesc, 1u);
           }
@@ -195,6 +199,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
         umma_commit<1>(&tfull[b]);
+        if (++b == static_cast<uint32_t>(p.tbufs)) { b = 0; bph ^= 1; }
       }
     }
     __syncwarp();
@@ -220,12 +225,14 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int full_mark = cap - static_cast<int>(round_tiles) * BLOCK_M;
     const uint32_t n_it = t_first < t_end ? static_cast<uint32_t>((t_end - t_first + gridDim.x - 1) / gridDim.x) : 0u;
     float tau_next = (eq < p.nq) ? tau_load(p.sink.tau_g, eq) : INFINITY;
+    // accumulator buffer and phase of this set's next tile (iter = set, set + 2, ...: round_tiles is even, so the sequence runs on
+    // across rounds), kept as running counters: iter % tbufs and iter / tbufs are runtime divisions otherwise
+    uint32_t b = static_cast<uint32_t>(set) % static_cast<uint32_t>(p.tbufs), bph = (static_cast<uint32_t>(set) / static_cast<uint32_t>(p.tbufs)) & 1u;
 
     for (uint32_t r0 = 0; r0 < n_it; r0 += round_tiles) {
       const uint32_t r1 = min(n_it, r0 + round_tiles);
       for (uint32_t iter = r0 + set; iter < r1; iter += EPI_SETS) {  // r0 is even: the parity of iter is the set
         const int64_t t = t_first + static_cast<int64_t>(iter) * gridDim.x;
-        const uint32_t b = iter % p.tbufs, bph = (iter / p.tbufs) & 1;
         const int64_t row = perm_tile(p.perm, t) * BLOCK_M + et;
         const bool row_ok = row < p.n;
         const float hn = (L2 && row_ok) ? p.half_norm[row] : 0.f;
@@ -257,6 +264,8 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
           }
         }
+        b += EPI_SETS;
+        while (b >= static_cast<uint32_t>(p.tbufs)) { b -= static_cast<uint32_t>(p.tbufs); bph ^= 1u; }
       }
       if (p.no_check) continue;
       // ---- end of a round: could any query's list overflow during the next round? ----

@@ -21,7 +21,7 @@
 
 namespace nxf {
 
-template <typename T, int LPR>
+template <typename T, int LPR, bool L2>
 __global__ void __launch_bounds__(mg::THREADS) subset_search_kernel(SubsetParams p) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   Entry* ent = reinterpret_cast<Entry*>(dyn_smem);                               // [MAXK] scored entries of a short list
@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(mg::THREADS) subset_search_kernel(SubsetParams
   const int64_t qi = blockIdx.x;
   const int tid = threadIdx.x;
   const int ld = static_cast<int>(p.ld);
-  const bool l2 = p.metric == NXF_METRIC_L2;
+  constexpr bool l2 = L2;
 
   int64_t off0 = p.offsets[qi], off1 = p.offsets[qi + 1];
   if (off0 < 0 || off1 < off0 || off1 > p.total || off1 - off0 > (int64_t(1) << 30)) {
@@ -89,14 +89,16 @@ __global__ void __launch_bounds__(mg::THREADS) subset_search_kernel(SubsetParams
         const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          dot0 = fmaf(qv[e], a[e], dot0); nn0 = fmaf(a[e], a[e], nn0);
-          dot1 = fmaf(qv[e], b[e], dot1); nn1 = fmaf(b[e], b[e], nn1);
+          dot0 = fmaf(qv[e], a[e], dot0);
+          dot1 = fmaf(qv[e], b[e], dot1);
+          if (L2) { nn0 = fmaf(a[e], a[e], nn0); nn1 = fmaf(b[e], b[e], nn1); }   // IP: half the FMAs (the kernel is close to issue bound)
         }
       }
 #pragma unroll
       for (int o = LPR / 2; o > 0; o >>= 1) {
-        dot0 += __shfl_xor_sync(kFullMask, dot0, o); nn0 += __shfl_xor_sync(kFullMask, nn0, o);
-        dot1 += __shfl_xor_sync(kFullMask, dot1, o); nn1 += __shfl_xor_sync(kFullMask, nn1, o);
+        dot0 += __shfl_xor_sync(kFullMask, dot0, o);
+        dot1 += __shfl_xor_sync(kFullMask, dot1, o);
+        if (L2) { nn0 += __shfl_xor_sync(kFullMask, nn0, o); nn1 += __shfl_xor_sync(kFullMask, nn1, o); }
       }
       if (l == 0) {
         // a row id outside the index is reported through p.err; it ranks behind everything
@@ -108,7 +110,8 @@ __global__ void __launch_bounds__(mg::THREADS) subset_search_kernel(SubsetParams
   __syncthreads();
 
   // ---- keep the best min(L, k_out) ----
-  const int keep = min(L, p.k_out);
+  // short lists are sorted whole (a bitonic sort of <= 512 keys costs fewer barriers than the four radix passes)
+  const int keep = (L <= 512) ? L : min(L, p.k_out);
   Entry* kept = reinterpret_cast<Entry*>(keys);
   const Entry* src = dst;
   if (L > keep) {
@@ -144,7 +147,7 @@ __global__ void __launch_bounds__(mg::THREADS) subset_search_kernel(SubsetParams
   for (int j = tid; j < p.k_out; j += mg::THREADS) {
     float s;
     int64_t pos;
-    if (j < keep) {
+    if (j < keep) {   // keep >= min(L, k_out)
       const uint64_t kk = keys[j];
       const float sc = sort_key_score(kk);
       s = l2 ? fmaxf(qn - 2.f * sc, 0.f) : sc;
@@ -162,11 +165,16 @@ int launch_subset_search(int store_dtype, const SubsetParams& p, int64_t nq, cud
   if (nq <= 0) return NXF_OK;
   const size_t smem = static_cast<size_t>(mg::MAXK) * 16 + static_cast<size_t>(p.ld) * 4;
   if (smem > 200 * 1024) { set_error("search_subsets: dim %d too large", p.dim); return NXF_EUNSUPPORTED; }
-#define NXF_LAUNCH_SUBSET2(T, LPR)                                                                                          \
-  do {                                                                                                                      \
-    if (smem > 48 * 1024)                                                                                                   \
-      NXF_CUDA(cudaFuncSetAttribute(subset_search_kernel<T, LPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    subset_search_kernel<T, LPR><<<static_cast<unsigned>(nq), mg::THREADS, smem, stream>>>(p);                              \
+#define NXF_LAUNCH_SUBSET3(T, LPR, L2)                                                                                          \
+  do {                                                                                                                          \
+    if (smem > 48 * 1024)                                                                                                       \
+      NXF_CUDA(cudaFuncSetAttribute(subset_search_kernel<T, LPR, L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    subset_search_kernel<T, LPR, L2><<<static_cast<unsigned>(nq), mg::THREADS, smem, stream>>>(p);                              \
+  } while (0)
+#define NXF_LAUNCH_SUBSET2(T, LPR)                                      \
+  do {                                                                  \
+    if (p.metric == NXF_METRIC_L2) NXF_LAUNCH_SUBSET3(T, LPR, true);    \
+    else NXF_LAUNCH_SUBSET3(T, LPR, false);                             \
   } while (0)
 #define NXF_LAUNCH_SUBSET(T)                          \
   do {                                                \
@@ -182,6 +190,7 @@ int launch_subset_search(int store_dtype, const SubsetParams& p, int64_t nq, cud
   }
 #undef NXF_LAUNCH_SUBSET
 #undef NXF_LAUNCH_SUBSET2
+#undef NXF_LAUNCH_SUBSET3
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
 }

@@ -79,7 +79,8 @@ def test_search_subsets_matches_oracle(store, d, lengths, k):
     D, P = idx.search_subsets(x, offsets, rows, k)
     assert idx.stats()["last_path_name"] == "subset"
     ref_D, ref_P, full = subset_oracle(stored(c, store), x, offsets, rows, k)
-    check_subsets(D, P, ref_D, ref_P, full, offsets)
+    # unnormalised N(0,1) vectors: |q||c| ~ d, so the fp32 summation error of a score near 0 is absolute, ~1e-7 * d
+    check_subsets(D, P, ref_D, ref_P, full, offsets, atol=1e-7 * d)
 
 
 def test_search_subsets_exact_ties_are_in_position_order():
@@ -94,7 +95,7 @@ def test_search_subsets_exact_ties_are_in_position_order():
     for k in (10, 200, 2048):
         D, P = idx.search_subsets(x, offsets, rows, k)
         ref_D, ref_P, full = subset_oracle(c, x, offsets, rows, k)
-        check_subsets(D, P, ref_D, ref_P, full, offsets)
+        check_subsets(D, P, ref_D, ref_P, full, offsets, atol=1e-5)
         for i in range(9):
             m = min(k, int(offsets[i + 1] - offsets[i]))
             r = rows[offsets[i]:offsets[i + 1]]
@@ -132,7 +133,7 @@ def test_search_subsets_device_resident_inputs_and_outputs():
     D, P = idx.search_subsets(torch.from_numpy(x).cuda(), torch.from_numpy(offsets).cuda(), torch.from_numpy(rows).cuda(), 10)
     assert D.is_cuda and P.is_cuda and D.dtype == torch.float32 and P.dtype == torch.int64
     ref_D, ref_P, full = subset_oracle(stored(c, "bf16"), x, offsets, rows, 10)
-    check_subsets(D.cpu().numpy(), P.cpu().numpy(), ref_D, ref_P, full, offsets)
+    check_subsets(D.cpu().numpy(), P.cpu().numpy(), ref_D, ref_P, full, offsets, atol=3e-5)
     # host lists with device queries, and the other way round
     D2, P2 = idx.search_subsets(torch.from_numpy(x).cuda(), offsets, rows, 10)
     np.testing.assert_array_equal(P2.cpu().numpy(), P.cpu().numpy())
