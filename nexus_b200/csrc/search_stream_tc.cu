@@ -146,43 +146,47 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 
   if (warp == 0) {
     // ============================== TMA producer ==============================
+    // All 32 lanes run the loop and wait on the barriers; lane 0 alone issues.  (With the loop inside `if (lane == 0)` the other 31
+    // lanes sit at the closing __syncwarp as a second, divergent instruction stream of the same warp and take a quarter of its issue
+    // turns -- measured on 128-byte rows, where this thread and the MMA issuer pace the whole stream.)
     if (lane == 0) {
       mbar_expect_tx(qfull, static_cast<uint32_t>(q_bytes));
       for (int kb = 0; kb < p.kblocks; ++kb) tma_load_2d(&tmap_q, qfull, q_smem + kb * p.nq_pad * 128, kb * BLOCK_K, 0, kEvictLast);
-      int s = 0;
-      uint32_t ph = 0;
-      for (int64_t t = t_first; t < t_end; t += gridDim.x) {
-        const int32_t row0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_M);
-        for (int kb = 0; kb < p.kblocks; ++kb) {
-          mbar_wait(&empty[s], ph ^ 1);
+    }
+    int s = 0;
+    uint32_t ph = 0;
+    for (int64_t t = t_first; t < t_end; t += gridDim.x) {
+      const int32_t row0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_M);
+      for (int kb = 0; kb < p.kblocks; ++kb) {
+        mbar_wait(&empty[s], ph ^ 1);
+        if (lane == 0) {
           mbar_expect_tx(&full[s], A_BYTES);
           tma_load_2d(&tmap_c, &full[s], ring + s * A_BYTES, kb * BLOCK_K, row0, kEvictFirst);
-          if (++s == p.stages) { s = 0; ph ^= 1; }
         }
+        if (++s == p.stages) { s = 0; ph ^= 1; }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // ============================== MMA issuer ==============================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M, p.nq_pad);
-      mbar_wait(qfull, 0);
-      tc_fence_after();
-      // This single thread paces the whole stream on short rows (one K block per tile: a tile every ~700 clocks at HBM speed), so
-      // its per-tile instruction chain is kept short: running counters instead of divisions, descriptors advanced by addition.
-      int s = 0;
-      uint32_t ph = 0;
-      uint32_t b = 0, bph = 0;
-      const uint64_t a_desc0 = umma_desc_sw128(smem_u32(ring));          // stage s: + s * (A_BYTES >> 4) in the address field
-      const uint64_t b_desc0 = umma_desc_sw128(smem_u32(q_smem));        // query block qb: + qb * (nq_pad * 128 >> 4)
-      const uint32_t q_blk = static_cast<uint32_t>(p.nq_pad) * 8u;
-      for (int64_t t = t_first; t < t_end; t += gridDim.x) {
-        mbar_wait(&tempty[b], bph ^ 1);
+    // Lane 0 paces the whole stream on short rows (one K block per tile: a tile every ~700 clocks at HBM speed), so the per-tile
+    // instruction chain is kept short: running counters instead of divisions, descriptors advanced by addition, warp-uniform loop.
+    const uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M, p.nq_pad);
+    mbar_wait(qfull, 0);
+    tc_fence_after();
+    int s = 0;
+    uint32_t ph = 0;
+    uint32_t b = 0, bph = 0;
+    const uint64_t a_desc0 = umma_desc_sw128(smem_u32(ring));          // stage s: + s * (A_BYTES >> 4) in the address field
+    const uint64_t b_desc0 = umma_desc_sw128(smem_u32(q_smem));        // query block qb: + qb * (nq_pad * 128 >> 4)
+    const uint32_t q_blk = static_cast<uint32_t>(p.nq_pad) * 8u;
+    for (int64_t t = t_first; t < t_end; t += gridDim.x) {
+      mbar_wait(&tempty[b], bph ^ 1);
+      const uint32_t d_tmem = tmem_base + b * p.tbuf_stride;
+      for (int kb = 0; kb < p.kblocks; ++kb) {
+        mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + b * p.tbuf_stride;
-        for (int kb = 0; kb < p.kblocks; ++kb) {
-          mbar_wait(&full[s], ph);
-          tc_fence_after();
+        if (lane == 0) {
           const uint64_t a_desc = a_desc0 + static_cast<uint32_t>(s) * static_cast<uint32_t>(A_BYTES >> 4);
           // split storage: corpus block kb of the hi plane meets q_hi[kb] and q_mid[kb]; of the mid plane, q_hi[kb - split_kb]
           const int qb = (p.split_kb > 0 && kb >= p.split_kb) ? kb - p.split_kb : kb;
@@ -196,11 +200,12 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) umma_f16<1>(d_tmem, a_desc + 2 * k4, b2_desc + 2 * k4, idesc, 1u);
           }
           umma_commit<1>(&empty[s]);
-          if (++s == p.stages) { s = 0; ph ^= 1; }
+          if (kb == p.kblocks - 1) umma_commit<1>(&tfull[b]);
         }
-        umma_commit<1>(&tfull[b]);
-        if (++b == static_cast<uint32_t>(p.tbufs)) { b = 0; bph ^= 1; }
+        __syncwarp();
+        if (++s == p.stages) { s = 0; ph ^= 1; }
       }
+      if (++b == static_cast<uint32_t>(p.tbufs)) { b = 0; bph ^= 1; }
     }
     __syncwarp();
   } else if (warp >= EPI_WARP0) {
