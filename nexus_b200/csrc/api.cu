@@ -851,13 +851,27 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       }
       kp.perm.finish();
       bounds[++n_pass] = P.n_tiles;
+      kp.est_only = 0;
+      // With two sample passes the first (about one tile per CTA) is estimate-only: the CTA's best score per query, the m-th
+      // largest of which over the CTAs seeds the threshold; its tiles are streamed again by the second pass, which starts from
+      // empty lists.  (Appending everything from -inf instead filled 128 lists per CTA, cost a 19 k-key selection per query
+      // in between and a prune of every list at the start of the next launch: 140 us of a 550 us search at 128 queries.)
+      const bool est_first = n_pass == 3 && env_int("NXF_K2T_EST", 1) != 0;
       for (int ps = 0; ps + 1 < n_pass; ++ps) {
-        kp.tile_begin = bounds[ps]; kp.tile_end = bounds[ps + 1];
-        kp.first_pass = ps == 0; kp.last_pass = 0; kp.no_check = (bounds[ps + 1] - bounds[ps] <= P.grid) ? 1 : 0;
+        const bool est = est_first && ps == 0;
+        kp.tile_begin = (est_first && ps == 1) ? 0 : bounds[ps]; kp.tile_end = bounds[ps + 1];
+        kp.first_pass = ps == 0 || (est_first && ps == 1); kp.last_pass = 0; kp.est_only = est ? 1 : 0;
+        kp.no_check = (est || kp.tile_end - kp.tile_begin <= P.grid) ? 1 : 0;
         rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
         if (rc) return rc;
+        kp.est_only = 0;
         const int m = std::min(P.k_fetch, sample_rank(P.k_fetch, bounds[ps + 1], P.n_tiles));
-        rc = launch_seed_tau_lists(cand, k2t_cnt, P.grid, kp.nq_pad, P.cap, m, tau_g, static_cast<int>(bn), stream);
+        if (est) {
+          // the m-th largest of min(grid, tiles) per-CTA maxima; more than that many is not available: leave the threshold alone
+          if (m <= std::min<int64_t>(P.grid, bounds[1])) rc = launch_seed_tau_est(k2t_cnt, P.grid, kp.nq_pad, m, tau_g, static_cast<int>(bn), stream);
+        } else {
+          rc = launch_seed_tau_lists(cand, k2t_cnt, P.grid, kp.nq_pad, P.cap, m, tau_g, static_cast<int>(bn), stream);
+        }
         if (rc) return rc;
         idx->stats.kernel_launches += 2;
       }

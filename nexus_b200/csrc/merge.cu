@@ -251,6 +251,42 @@ __global__ void __launch_bounds__(mg::THREADS) seed_tau_lists_kernel(const Entry
   if (tid == 0) atomicMax(&tau_g[q], T);
 }
 
+// K2T's estimate pass leaves one key per (CTA, query) in est_g: the best score among the rows that CTA streamed.  The m-th
+// largest of those maxima is a lower bound of the m-th best score of the streamed sample (m different rows reach it), hence --
+// for m = sample_rank() -- of the k'-th best of the whole corpus with the usual probability; verified after the main pass like
+// every sampled threshold.  One warp per query, bitwise descent on the keys (<= 8 per lane).
+__global__ void __launch_bounds__(256) seed_tau_est_kernel(const uint32_t* __restrict__ est_g, int grid, int nq_pad, int m, uint32_t* tau_g, int nq) {
+  const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (q >= nq) return;  // whole warps
+  const int lane = threadIdx.x & 31;
+  uint32_t key[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int b = lane + 32 * j;
+    key[j] = b < grid ? est_g[static_cast<int64_t>(b) * nq_pad + q] : 0u;
+  }
+  uint32_t prefix = 0;
+#pragma unroll 1
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t cand = prefix | (1u << bit);
+    uint32_t c = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) c += key[j] >= cand ? 1u : 0u;
+    c = __reduce_add_sync(0xFFFFFFFFu, c);
+    if (c >= static_cast<uint32_t>(m)) prefix = cand;
+  }
+  // prefix = the m-th largest key (0 when fewer than m CTAs saw a row); -inf and below leave the threshold alone
+  if (lane == 0 && prefix > kKeyNegInf) atomicMax(&tau_g[q], prefix);
+}
+
+int launch_seed_tau_est(const uint32_t* est_g, int grid, int nq_pad, int m, uint32_t* tau_g, int nq, cudaStream_t stream) {
+  if (nq <= 0) return NXF_OK;
+  if (grid > 256) { set_error("seed: %d CTAs per query (max 256)", grid); return NXF_EUNSUPPORTED; }
+  seed_tau_est_kernel<<<static_cast<unsigned>((nq * 32 + 255) / 256), 256, 0, stream>>>(est_g, grid, nq_pad, m, tau_g, nq);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
 int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g, int nq,
                           cudaStream_t stream) {
   if (nq <= 0) return NXF_OK;

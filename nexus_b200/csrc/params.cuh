@@ -112,6 +112,7 @@ struct K2TParams {
   int first_pass;   // lists start empty
   int last_pass;    // lists are reduced to k' and flushed to the arena at the end (else: lengths stored to cnt_g)
   int no_check;     // one tile per CTA (<= 128 entries per list, below cap): skip the overflow checks
+  int est_only;     // estimate pass: nothing is appended, the CTA's best score per query goes to cnt_g (as a monotone key) instead
   const float* half_norm;
   SinkParams sink;
 };
@@ -176,6 +177,7 @@ size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages);
 int k2t_plan_stages(int kblocks, int nq_pad);
 int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g, int nq,
                           cudaStream_t stream);
+int launch_seed_tau_est(const uint32_t* est_g, int grid, int nq_pad, int m, uint32_t* tau_g, int nq, cudaStream_t stream);
 int launch_select_tau(Entry* arena, uint32_t* qcnt, int64_t arena_stride, int m, uint32_t* tau_g, int64_t nq, int reset, cudaStream_t stream);
 int launch_verify_counts(uint32_t* qcnt, uint32_t* tau_g, int64_t nq, int need, uint32_t* flag, cudaStream_t stream);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);

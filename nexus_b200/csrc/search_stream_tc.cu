@@ -97,6 +97,21 @@ __device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], int ch, floa
   }
 }
 
+// Estimate pass: nothing is appended; the best score of this CTA's rows per query is kept (as a monotone key) in est_s.
+// One REDUX.MAX per query and warp, lane j keeps query j's maximum, 16 shared-memory atomics per slice.
+template <bool L2>
+__device__ __forceinline__ void k2t_chunk_est(const uint32_t (&vr)[16], int ch, float hn, bool row_ok, uint32_t* __restrict__ est_s,
+                                              unsigned lane) {
+  uint32_t mine = 0;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float v = L2 ? __uint_as_float(vr[j]) - hn : __uint_as_float(vr[j]);
+    const uint32_t m = __reduce_max_sync(kFullMask, row_ok ? okey(v) : 0u);
+    if (lane == static_cast<unsigned>(j)) mine = m;
+  }
+  if (lane < 16) atomicMax(&est_s[ch * 16 + lane], mine);
+}
+
 template <bool BF16, bool L2>
 __global__ void __launch_bounds__(k2t::THREADS, 1)
 k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K2TParams p) {
@@ -257,7 +272,8 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[b]);
           }
-          k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+          if (p.est_only) k2t_chunk_est<L2>(va, ch, hn, row_ok, reinterpret_cast<uint32_t*>(cnt_s), lane);
+          else k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
           if (more) {
             tmem_ld_wait_dep16(vb);
             if (ch + 2 < chunks) tmem_ld16(tbase + (ch + 2) * 16, va);
@@ -266,7 +282,8 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
               __syncwarp();
               if (lane == 0) mbar_arrive(&tempty[b]);
             }
-            k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+            if (p.est_only) k2t_chunk_est<L2>(vb, ch + 1, hn, row_ok, reinterpret_cast<uint32_t*>(cnt_s), lane);
+            else k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
           }
         }
         b += EPI_SETS;
