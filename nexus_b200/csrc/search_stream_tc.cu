@@ -63,15 +63,24 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("barrier.cta.sync.
 static_assert(k2t::EPI_THREADS == 256, "the named barrier above counts 256 threads");
 
 // One 16-query slice of a corpus row's scores: d = v - tau on a max tree; the common case is one compare, branch not taken.
+// The thresholds of the slice are passed in (loaded by the caller BEFORE it waits for the TMEM load, so that the two latencies
+// overlap), and the maximum is a balanced tree of depth 3 -- with two epilogue warps per sub-partition it is dependent-issue
+// latency, not issue slots, that bounds this loop at 128 queries.
+struct TauSlice { float4 t[4]; };
+__device__ __forceinline__ TauSlice k2t_load_tau(const float* __restrict__ tau_s, int ch) {
+  TauSlice r;
+  const float4* tp = reinterpret_cast<const float4*>(tau_s + ch * 16);  // same address for every lane: broadcast
+#pragma unroll
+  for (int j4 = 0; j4 < 4; ++j4) r.t[j4] = tp[j4];
+  return r;
+}
 template <bool L2>
-__device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], int ch, float hn, int64_t row, bool row_ok,
-                                          const float* __restrict__ tau_s, int* __restrict__ cnt_s,
-                                          uint32_t* __restrict__ cand_words, int cap) {
+__device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], const TauSlice& ts, int ch, float hn, int64_t row, bool row_ok,
+                                          int* __restrict__ cnt_s, uint32_t* __restrict__ cand_words, int cap) {
   float v[16], d[16];
-  const float4* tp = reinterpret_cast<const float4*>(tau_s + ch * 16);
 #pragma unroll
   for (int j4 = 0; j4 < 4; ++j4) {
-    const float4 tq = tp[j4];  // same address for every lane: broadcast
+    const float4 tq = ts.t[j4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) v[4 * j4 + e] = L2 ? __uint_as_float(vr[4 * j4 + e]) - hn : __uint_as_float(vr[4 * j4 + e]);
     d[4 * j4] = v[4 * j4] - tq.x;
@@ -79,10 +88,9 @@ __device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], int ch, floa
     d[4 * j4 + 2] = v[4 * j4 + 2] - tq.z;
     d[4 * j4 + 3] = v[4 * j4 + 3] - tq.w;
   }
-  float m = fmax3(d[0], d[1], d[2]);
-#pragma unroll
-  for (int j = 3; j < 15; j += 2) m = fmax3(m, d[j], d[j + 1]);
-  m = fmaxf(m, d[15]);
+  const float m0 = fmax3(d[0], d[1], d[2]), m1 = fmax3(d[3], d[4], d[5]), m2 = fmax3(d[6], d[7], d[8]);
+  const float m3 = fmax3(d[9], d[10], d[11]), m4 = fmax3(d[12], d[13], d[14]);
+  const float m = fmax3(fmax3(m0, m1, m2), fmaxf(m3, m4), d[15]);
   if (m > 0.f && row_ok) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
@@ -264,6 +272,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         tmem_ld16(tbase, va);
 #pragma unroll 1
         for (int ch = 0; ch < chunks; ch += 2) {
+          const TauSlice ta = k2t_load_tau(tau_s, ch);
           tmem_ld_wait_dep16(va);
           const bool more = ch + 1 < chunks;
           if (more) tmem_ld16(tbase + (ch + 1) * 16, vb);
@@ -273,8 +282,9 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             if (lane == 0) mbar_arrive(&tempty[b]);
           }
           if (p.est_only) k2t_chunk_est<L2>(va, ch, hn, row_ok, reinterpret_cast<uint32_t*>(cnt_s), lane);
-          else k2t_chunk<L2>(va, ch, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+          else k2t_chunk<L2>(va, ta, ch, hn, row, row_ok, cnt_s, cand_words, cap);
           if (more) {
+            const TauSlice tb = k2t_load_tau(tau_s, ch + 1);
             tmem_ld_wait_dep16(vb);
             if (ch + 2 < chunks) tmem_ld16(tbase + (ch + 2) * 16, va);
             else {
@@ -283,7 +293,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
               if (lane == 0) mbar_arrive(&tempty[b]);
             }
             if (p.est_only) k2t_chunk_est<L2>(vb, ch + 1, hn, row_ok, reinterpret_cast<uint32_t*>(cnt_s), lane);
-            else k2t_chunk<L2>(vb, ch + 1, hn, row, row_ok, tau_s, cnt_s, cand_words, cap);
+            else k2t_chunk<L2>(vb, tb, ch + 1, hn, row, row_ok, cnt_s, cand_words, cap);
           }
         }
         b += EPI_SETS;

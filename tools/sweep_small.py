@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--nqs", default="1,2,4,8,32,128")
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--store", default="", help="override the storage dtype (f32 | bf16 | f16)")
+    ap.add_argument("--flags", type=int, default=0, help="NXF_SEARCH_* flags (4 = force K1, 32 = force K2T, 2 = force K2)")
     a = ap.parse_args()
     import torch
     from nexus_b200 import FlatIndex
@@ -30,6 +31,7 @@ def main():
     dev = torch.device("cuda", 0)
     idx = FlatIndex(D, "ip", store, device=0)
     idx.reserve(N)
+    idx.search_flags = a.flags
     bench.build_shard(torch, idx, 0, N, D, store, norm, dev)
     g = torch.Generator(device=dev)
     g.manual_seed(2002)
