@@ -486,6 +486,7 @@ struct SearchPlan {
   int split = 0;     // K1 over the two-plane bf16 shadow of fp32 rows
   int seed = 0;      // K2T: threshold-seeding pass over the first tile of every CTA
   int cap = 0;
+  int epi_sets = 2;
   int grid = 0;
   int num_qt = 0, chunks = 1;
   int64_t tiles_per_chunk = 1, n_tiles = 0;
@@ -584,7 +585,12 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(idx->sm_count, P.n_tiles)));
     // overflow checks every `ce` tiles: short rows (few K blocks per tile) cannot afford a barrier per tile
     P.rw = std::max(1, std::min(8, 16 / std::max<int>(1, static_cast<int>(idx->ld / 64) * (P.split ? 2 : 1))));
-    P.cap = 2 * P.k_fetch + 2 * 128 * P.rw;   // pruned once more than 2k' entries are held
+    // epilogue warp sets: two while the filter keeps up, three / four once it is latency bound (search_stream_tc.cu); NXF_K2T_SETS=2..4 overrides
+    {
+      const int64_t nqp = round_up64(nq, 16);
+      P.epi_sets = std::max(2, std::min(4, env_int("NXF_K2T_SETS", nqp <= 32 ? 2 : (nqp <= 96 ? 3 : 4))));
+    }
+    P.cap = 2 * P.k_fetch + P.epi_sets * 128 * P.rw;   // pruned once more than 2k' entries are held (one round of appends on top)
     P.owners = static_cast<int64_t>(P.grid) * P.nq_t;
     // threshold seeding (DESIGN.md "K2T"): one tile per CTA first, whole lists (<= 128 entries) into the arena, the sample's k'-th best
     // into tau_g; pays off once every CTA streams many tiles (NXF_K2T_SEED=0/1 overrides)
@@ -822,6 +828,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.tbufs = std::min(8, 512 / kp.tbuf_stride);
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.check_every = P.rw;
+      kp.epi_sets = P.epi_sets;
       kp.sink = sink;
       kp.sink.cap = P.cap;
       const void* c_rows = P.split ? idx->split : idx->data;

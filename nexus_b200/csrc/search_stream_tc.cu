@@ -22,9 +22,11 @@ constexpr int BLOCK_M = 128;   // corpus rows per tile
 constexpr int BLOCK_K = 64;
 constexpr int UMMA_K = 16;
 constexpr int EPI_WARP0 = 4;
-constexpr int EPI_SETS = 2;                    // two epilogue warps per SM sub-partition: set s filters tiles s, s + 2, ...
-constexpr int EPI_THREADS = 128 * EPI_SETS;
-constexpr int THREADS = 128 + EPI_THREADS;
+// Epilogue warp sets (template parameter SETS = 2..4, four warps each, one per SM sub-partition): set s filters tiles s, s + SETS, ...
+// Few queries: two sets keep up and leave the issue slots of sub-partitions 0/1 to the producer and the MMA issuer (one query on
+// 128-byte rows: 0.218 ms with two sets, 0.244 ms with three); from ~64 queries on the per-tile filter is bound by dependent-issue
+// latency and more sets hide it (128 queries: 0.439 ms with two, 0.366 with three, 0.342 with four -- at 102 registers per thread).
+constexpr int threads(int sets) { return 128 + 128 * sets; }
 constexpr int TMEM_COLS = 512;
 constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB per stage
 constexpr int MAX_STAGES = 12;
@@ -49,18 +51,19 @@ __device__ __forceinline__ void tmem_ld_wait_dep16(uint32_t (&r)[16]) {
                :
                : "memory");
 }
-// named barrier 1 over the 256 epilogue threads with an OR reduction of a predicate
+// named barrier 1 over the epilogue threads with an OR reduction of a predicate
+template <int SETS>
 __device__ __forceinline__ bool epi_bar_or(bool pred) {
   uint32_t r;
   asm volatile(
       "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 p, %1, 0;\n\t"
-      "barrier.cta.red.or.pred.aligned q, 1, 256, p;\n\t"
+      "barrier.cta.red.or.pred.aligned q, 1, %2, p;\n\t"
       "selp.u32 %0, 1, 0, q;\n\t}"
-      : "=r"(r) : "r"(static_cast<uint32_t>(pred)) : "memory");
+      : "=r"(r) : "r"(static_cast<uint32_t>(pred)), "n"(128 * SETS) : "memory");
   return r != 0;
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("barrier.cta.sync.aligned 1, 256;" ::: "memory"); }
-static_assert(k2t::EPI_THREADS == 256, "the named barrier above counts 256 threads");
+template <int SETS>
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("barrier.cta.sync.aligned 1, %0;" ::"n"(128 * SETS) : "memory"); }
 
 // One 16-query slice of a corpus row's scores: d = v - tau on a max tree; the common case is one compare, branch not taken.
 // The thresholds of the slice are passed in (loaded by the caller BEFORE it waits for the TMEM load, so that the two latencies
@@ -120,10 +123,11 @@ __device__ __forceinline__ void k2t_chunk_est(const uint32_t (&vr)[16], int ch, 
   if (lane < 16) atomicMax(&est_s[ch * 16 + lane], mine);
 }
 
-template <bool BF16, bool L2>
-__global__ void __launch_bounds__(k2t::THREADS, 1)
+template <bool BF16, bool L2, int SETS>
+__global__ void __launch_bounds__(k2t::threads(SETS), 1)
 k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K2TParams p) {
   using namespace k2t;
+  constexpr int EPI_SETS = SETS;
   extern __shared__ unsigned char smem_raw[];
   // 1024-byte alignment by pointer arithmetic on the shared array itself (an integer round trip would make every later access generic)
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -247,7 +251,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     Entry* cta_cand = p.sink.cand + static_cast<int64_t>(blockIdx.x) * p.nq_pad * cap;  // [nq_pad][cap]
     uint32_t* cand_words = reinterpret_cast<uint32_t*>(cta_cand);
     const int chunks = p.nq_pad / 16;
-    const uint32_t round_tiles = 2u * static_cast<uint32_t>(p.check_every);  // tiles between two overflow checks / threshold refreshes
+    const uint32_t round_tiles = static_cast<uint32_t>(EPI_SETS) * static_cast<uint32_t>(p.check_every);  // tiles between two overflow checks / threshold refreshes
     // a list gains <= 128 entries per tile, i.e. <= 128 * round_tiles between two checks, and the counts read at a check are
     // exact (every appender has arrived at the barrier): cap - full_mark = one round of appends
     const int full_mark = cap - static_cast<int>(round_tiles) * BLOCK_M;
@@ -259,7 +263,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 
     for (uint32_t r0 = 0; r0 < n_it; r0 += round_tiles) {
       const uint32_t r1 = min(n_it, r0 + round_tiles);
-      for (uint32_t iter = r0 + set; iter < r1; iter += EPI_SETS) {  // r0 is even: the parity of iter is the set
+      for (uint32_t iter = r0 + set; iter < r1; iter += EPI_SETS) {  // r0 is a multiple of EPI_SETS: iter % EPI_SETS is the set
         const int64_t t = t_first + static_cast<int64_t>(iter) * gridDim.x;
         const int64_t row = perm_tile(p.perm, t) * BLOCK_M + et;
         const bool row_ok = row < p.n;
@@ -301,7 +305,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
       if (p.no_check) continue;
       // ---- end of a round: could any query's list overflow during the next round? ----
-      const bool any_full = epi_bar_or(eq < p.nq && cnt_s[eq] > full_mark);
+      const bool any_full = epi_bar_or<SETS>(eq < p.nq && cnt_s[eq] > full_mark);
       if (any_full) {
         for (int qi = ew8; qi < p.nq; qi += 4 * EPI_SETS) {  // warp w prunes queries w, w+8, ...
           const int n_q = cnt_s[qi];
@@ -315,7 +319,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             __syncwarp();
           }
         }
-        epi_bar_sync();
+        epi_bar_sync<SETS>();
       }
       // other CTAs' progress: thread eq looks after query eq (value loaded one round ago)
       if (eq < p.nq) {
@@ -326,7 +330,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 
     // ---- end of the launch: the last one reduces every list to k' and flushes it to the arena; the others only record the
     // list lengths (the lists stay where they are for the seed kernel and the next launch) ----
-    epi_bar_sync();
+    epi_bar_sync<SETS>();
     if (!p.last_pass) {
       if (eq < p.nq) p.cnt_g[static_cast<int64_t>(blockIdx.x) * p.nq_pad + eq] = static_cast<uint32_t>(cnt_s[eq]);
     } else {
@@ -377,16 +381,24 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* co
   if (rc) return rc;
   const size_t smem = k2t_smem_bytes(p.kblocks, p.nq_pad, p.stages);
   const bool l2 = p.half_norm != nullptr;
-#define NXF_K2T_LAUNCH(B, L)                                                                                                          \
+#define NXF_K2T_LAUNCH3(B, L, S)                                                                                                      \
   do {                                                                                                                                \
-    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));     \
-    k2t_stream_kernel<B, L><<<grid, k2t::THREADS, smem, stream>>>(tq, tc, p);                                                         \
+    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));  \
+    k2t_stream_kernel<B, L, S><<<grid, k2t::threads(S), smem, stream>>>(tq, tc, p);                                                   \
   } while (0)
+#define NXF_K2T_LAUNCH(B, L)                     \
+  do {                                           \
+    if (p.epi_sets == 2) NXF_K2T_LAUNCH3(B, L, 2);      \
+    else if (p.epi_sets == 3) NXF_K2T_LAUNCH3(B, L, 3); \
+    else NXF_K2T_LAUNCH3(B, L, 4);                      \
+  } while (0)
+  if (p.epi_sets < 2 || p.epi_sets > 4) { set_error("k2t: %d epilogue sets (2..4)", p.epi_sets); return NXF_EINVAL; }
   if (bf16 && l2) NXF_K2T_LAUNCH(true, true);
   else if (bf16) NXF_K2T_LAUNCH(true, false);
   else if (l2) NXF_K2T_LAUNCH(false, true);
   else NXF_K2T_LAUNCH(false, false);
 #undef NXF_K2T_LAUNCH
+#undef NXF_K2T_LAUNCH3
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
 }
