@@ -91,6 +91,17 @@ class IndexFlatL2(_LazyFlat):
         super().__init__(d, METRIC_L2)
 
 
+class IndexIVFFlat(_LazyFlat):
+    """``faiss.IndexIVFFlat(quantizer, d, nlist, metric)`` as the recsys index builder constructs it
+    (Nexus/inference/utils.py:19-22: ``IndexFlatIP`` quantizer, nlist = 100, ``METRIC_INNER_PRODUCT``), served by the exact
+    flat scan: every list is probed, so the result is what IVF returns at ``nprobe = nlist`` -- a recall superset of any
+    smaller ``nprobe`` (settable and ignored, recommendation/base.py:117).  Faiss's default metric for this class is L2."""
+
+    def __init__(self, quantizer, d: int, nlist: int = 100, metric: int = METRIC_L2):
+        super().__init__(int(d), int(metric))
+        self.quantizer, self.nlist = quantizer, int(nlist)
+
+
 def index_factory(d: int, description: str = "Flat", metric: int = METRIC_INNER_PRODUCT):
     desc = description.strip()
     if desc != "Flat" and not re.match(r"^(IVF\d+,)?Flat$", desc):
@@ -183,6 +194,45 @@ def read_index(path: str):
         return idx
     raise ValueError(f"read_index: {path} is neither a nexus_b200 flat index nor a .npy embedding cache "
                      "(native Faiss files are not readable without Faiss)")
+
+
+def load_embedding_cache(path: str):
+    """The embedding caches the reference writes, as ``(rows, ids)`` without touching the GPU:
+
+    * ``.npy``  -- ``doc.npy`` / ``corpus_embeddings.npy`` (text_retrieval/searcher.py:126-127,144; memory-mapped) -> ``(rows, None)``
+    * ``.pt``   -- ``item_vectors.pt`` = ``{'item_vectors': [N, D], 'item_ids': [N]}`` (training/.../trainer.py:38-39, read by
+                   Nexus/inference/utils.py:9-12) -> ``(rows, item_ids)``
+    * pickle    -- MMEB: an ``np.ndarray [Nq, D]`` (queries) or ``{candidate id: [D]}`` (eval_embedding.py:269-270,309-310,337-340)
+                   -> ``(rows, None)`` / ``(rows, list of keys in dictionary order)``
+    """
+    with open(path, "rb") as f:
+        head = f.read(8)
+    if head[:6] == b"\x93NUMPY":
+        return np.load(path, mmap_mode="r"), None
+    if head[:2] == b"PK" or path.endswith(".pt"):
+        import torch
+        data = torch.load(path, map_location="cpu")                      # utils.py:9
+        if not (isinstance(data, dict) and "item_vectors" in data):
+            raise ValueError(f"{path}: a .pt cache must hold {{'item_vectors', 'item_ids'}} (got {type(data).__name__})")
+        ids = data.get("item_ids")
+        return data["item_vectors"].detach().cpu().numpy(), (ids.cpu().numpy() if ids is not None else None)   # :11-13
+    import pickle
+    with open(path, "rb") as f:
+        obj = pickle.load(f)                                             # eval_embedding.py:338,340
+    if isinstance(obj, dict):
+        keys = list(obj.keys())
+        if not keys:
+            raise ValueError(f"{path}: empty candidate dictionary")
+        return np.stack([np.asarray(obj[k]) for k in keys]), keys        # :353-354
+    return np.asarray(obj), None
+
+
+def index_from_cache(path: str, metric: int = METRIC_INNER_PRODUCT):
+    """``(index, ids)``: a flat index over the rows of an embedding cache file (see :func:`load_embedding_cache`)."""
+    rows, ids = load_embedding_cache(path)
+    idx = _LazyFlat(int(rows.shape[1]), metric)
+    idx.add(np.ascontiguousarray(rows))
+    return idx, ids
 
 
 def install_as_faiss(force: bool = False) -> types.ModuleType:

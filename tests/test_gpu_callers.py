@@ -55,3 +55,32 @@ def test_positive_rank_errors_are_loud():
         positive_rank(torch.zeros(3), torch.zeros(3, 4))
     with pytest.raises(ValueError):
         positive_rank(torch.zeros(2).cuda(), torch.zeros(3, 4).cuda())
+
+
+def test_recsys_item_index_flow_from_item_vectors_pt(tmp_path):
+    """Nexus/inference/utils.py:8-25 (gen_item_index) and recommendation/base.py:114-117,182 on the shim: item_vectors.pt ->
+    IndexIVFFlat(quantizer, d, 100, IP) -> train/add -> write_index -> read_index -> nprobe -> search -> item_ids[I].
+    The exact scan must return the true top-k (what IVF returns when every list is probed)."""
+    import torch
+    from nexus_b200 import faiss_shim as F
+    rng = np.random.default_rng(21)
+    items = rng.standard_normal((5000, 64)).astype(np.float32)
+    item_ids = rng.permutation(100000)[:5000].astype(np.int64)
+    torch.save({"item_vectors": torch.from_numpy(items), "item_ids": torch.from_numpy(item_ids)}, tmp_path / "item_vectors.pt")
+    rows, ids = F.load_embedding_cache(str(tmp_path / "item_vectors.pt"))
+    quantizer = F.IndexFlatIP(rows.shape[1])
+    index = F.IndexIVFFlat(quantizer, rows.shape[1], 100, F.METRIC_INNER_PRODUCT)
+    index.train(rows)
+    index.add(rows)
+    F.write_index(index, str(tmp_path / "item.index"))
+    served = F.read_index(str(tmp_path / "item.index"))
+    served.nprobe = 10
+    users = rng.standard_normal((128, 64)).astype(np.float32)
+    D, I = served.search(users, 50)
+    ref_s, ref_i = oracle.blocked_ip_search(items, users, 50)
+    rep = oracle.check_topk(ref_s, ref_i, D, I, items, users, rtol=1e-5, atol=1e-5)
+    assert rep.ok, rep.messages[:5]
+    np.testing.assert_array_equal(ids[I][:, 0], item_ids[ref_i[:, 0]])
+    idx2, ids2 = F.index_from_cache(str(tmp_path / "item_vectors.pt"))
+    D2, I2 = idx2.search(users, 50)
+    np.testing.assert_array_equal(I2, I)

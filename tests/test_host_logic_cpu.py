@@ -126,3 +126,42 @@ def test_tile_permutation_is_a_bijection_with_spread_samples(n_tiles, s, s0):
     if s0 > 1:
         assert all(p % (s * s0) == 0 for p in phys[:n0])          # its first level: every (s*s0)-th tile
     assert phys[ns:] == sorted(phys[ns:])                         # everything else in corpus order
+
+
+def test_load_embedding_cache_formats(tmp_path):
+    """The cache files the reference writes: .npy, item_vectors.pt, MMEB pickles -- host parsing only."""
+    import pickle
+    import torch
+    from nexus_b200 import faiss_shim as F
+    rng = np.random.default_rng(0)
+    rows = rng.standard_normal((7, 16)).astype(np.float32)
+    np.save(tmp_path / "doc.npy", rows)                                                   # searcher.py:126-127
+    r, ids = F.load_embedding_cache(str(tmp_path / "doc.npy"))
+    assert ids is None and np.array_equal(np.asarray(r), rows)
+    torch.save({"item_vectors": torch.from_numpy(rows), "item_ids": torch.arange(100, 107)}, tmp_path / "item_vectors.pt")   # trainer.py:38-39
+    r, ids = F.load_embedding_cache(str(tmp_path / "item_vectors.pt"))
+    assert np.array_equal(r, rows) and ids.tolist() == list(range(100, 107))
+    with open(tmp_path / "qry.pkl", "wb") as f:
+        pickle.dump(rows, f)                                                              # eval_embedding.py:269-270
+    r, ids = F.load_embedding_cache(str(tmp_path / "qry.pkl"))
+    assert ids is None and np.array_equal(r, rows)
+    d = {f"c{i}": rows[i] for i in (3, 1, 5)}
+    with open(tmp_path / "cand.pkl", "wb") as f:
+        pickle.dump(d, f)                                                                 # eval_embedding.py:309-310
+    r, ids = F.load_embedding_cache(str(tmp_path / "cand.pkl"))
+    assert ids == ["c3", "c1", "c5"] and np.array_equal(r, rows[[3, 1, 5]])               # dictionary order, :353-354
+    torch.save({"something": 1}, tmp_path / "other.pt")
+    with pytest.raises(ValueError):
+        F.load_embedding_cache(str(tmp_path / "other.pt"))
+
+
+def test_ivfflat_constructor_shape():
+    """Nexus/inference/utils.py:19-20: IndexFlatIP quantizer + IndexIVFFlat(quantizer, d, 100, METRIC_INNER_PRODUCT); no device
+    is touched until the first add."""
+    from nexus_b200 import faiss_shim as F
+    quantizer = F.IndexFlatIP(32)
+    index = F.IndexIVFFlat(quantizer, 32, 100, F.METRIC_INNER_PRODUCT)
+    assert index.d == 32 and index.nlist == 100 and index.ntotal == 0 and index.is_trained
+    index.nprobe = 10                      # recommendation/base.py:117: settable, ignored
+    index.train(np.zeros((4, 32), np.float32))
+    assert F.IndexIVFFlat(quantizer, 32, 100).metric_type == F.METRIC_L2   # Faiss's default metric for this class
