@@ -204,9 +204,9 @@ void parallel_memcpy(unsigned char* dst, const unsigned char* src, size_t bytes,
   for (auto& x : th) x.join();
 }
 
-int64_t k1_arena_stride(int64_t clusters, int64_t num_qt, int k_fetch) {
+int64_t k1_arena_stride(int64_t clusters, int64_t num_qt, int k_fetch, int epi_sets) {
   const int64_t owners_max = std::min<int64_t>(clusters, (clusters + num_qt - 1) / std::max<int64_t>(num_qt, 1) + 1);
-  return (owners_max + 1) * k_fetch;
+  return (owners_max * epi_sets + 1) * k_fetch;  // every epilogue set of an owning cluster flushes its own list
 }
 
 // Rank m in a sample of `s_tiles` of `n_tiles` corpus tiles whose score is, except with probability < e^-30 per query, exceeded by
@@ -657,10 +657,15 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.chunks = static_cast<int>(ceil_div64(std::max<int64_t>(P.n_tiles, 1), P.round_tiles));  // reported as "chunks": rounds per launch
     // pruned between tiles once fewer than 256 (one tile of appends) slots are left
     P.cap = std::max(2, env_int("NXF_K1_CAP_MULT", 2)) * P.k_fetch + 256;
-    P.owners = static_cast<int64_t>(P.grid) * 128 * 2;  // two query-tile slots per CTA
+    // a second epilogue warp set when a tile holds too few K blocks for one set to hide behind the MMAs (search_tc.cu); NXF_K1_SETS=1/2 overrides
+    {
+      const int kb_tile = static_cast<int>(idx->ld / 64) * (P.split ? 3 : 1);
+      P.epi_sets = std::max(1, std::min(2, env_int("NXF_K1_SETS", kb_tile <= 6 ? 2 : 1)));
+    }
+    P.owners = static_cast<int64_t>(P.grid) * 128 * 2 * P.epi_sets;  // two query-tile slots per CTA, one buffer per (slot, set, row)
     // arena slice of a query: the list left by the sample passes (<= k' entries) + up to k' entries from every cluster that owns
     // a piece of the query tile in the last pass
-    P.arena_stride = k1_arena_stride(used, P.num_qt, P.k_fetch);
+    P.arena_stride = k1_arena_stride(used, P.num_qt, P.k_fetch, P.epi_sets);
   }
   return NXF_OK;
 }
@@ -737,7 +742,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     const int64_t rem = nq % batch;
     const int64_t nqt = ceil_div64(rem, 128 * P.cta_group);
     const int64_t cl = std::max<int64_t>(1, std::min<int64_t>(P.grid / P.cta_group, nqt * P.n_tiles));
-    rem_stride = k1_arena_stride(cl, nqt, P.k_fetch);
+    rem_stride = k1_arena_stride(cl, nqt, P.k_fetch, P.epi_sets);
     rem_arena = rem * rem_stride;
   }
 
@@ -912,6 +917,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
       kp.split_kb = 0;
       if (P.split) { kp.split_kb = kp.kblocks; kp.kblocks *= 3; }
       kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group));
+      kp.epi_sets = P.epi_sets;
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
       kp.sink = sink;

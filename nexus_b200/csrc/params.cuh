@@ -65,6 +65,7 @@ struct K1Params {
   int split_kb; // 0, or (fp32 storage as two bf16 planes [hi | mid] per row, each split_kb blocks wide) the plane width: the three
                 // segments of a tile are (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
   int num_qt;   // query tiles of 128*CG rows (<= number of clusters)
+  int epi_sets; // 1 or 2 epilogue warp sets (set s filters accumulator buffer s); 2 when a tile holds too few K blocks to hide one set
   int64_t tile_begin, tile_end;  // (virtual) corpus tiles [begin, end) of this pass (a search is 1-3 passes: sample, sample, rest)
   TilePerm perm;
   const uint32_t* run_flag;  // not NULL: the launch does nothing unless *run_flag != 0 (the fall-back pass after a failed verification)

@@ -151,8 +151,12 @@ __device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0,
   return rp;
 }
 
-template <int CG, bool BF16>
-__global__ void __launch_bounds__(k1::THREADS, 1)
+// SETS = epilogue warp sets.  One set (four warps, one per SM sub-partition) filters a 256 x 256 tile in ~3 600 clocks, bound by
+// dependent-issue latency; the MMAs of a tile take 512 clocks per K block, so from 7 K blocks on (D >= 448) one set hides behind the
+// tensor pipe.  Shorter rows get a second set on the other TMEM buffer (set s filters the tiles with iter % 2 == s), with its own
+// per-row thresholds, counters and candidate buffers -- to the rest of the search it is one more owner of the query.
+template <int CG, bool BF16, int SETS>
+__global__ void __launch_bounds__(128 + 128 * SETS, 1)
 k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K1Params p) {
   using namespace k1;
   using C = Cfg<CG>;
@@ -286,7 +290,8 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     __syncwarp();
   } else if (warp >= EPI_WARP0) {
     // ============================== epilogue ==============================
-    const int ew = warp - EPI_WARP0;  // == warp % 4: the TMEM lane quarter this warp may read
+    const int ew = (warp - EPI_WARP0) & 3;  // == warp % 4: the TMEM lane quarter this warp may read
+    const uint32_t set = static_cast<uint32_t>(warp - EPI_WARP0) >> 2;  // 0 .. SETS-1
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
     const int cap = p.sink.cap;
     const int k = p.sink.k;
@@ -295,7 +300,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     // this cluster's (at most two) query tiles: slot 0 = qt_base, slot 1 = qt_base + 1
     const int64_t qt_base = cluster_id * p.num_qt / num_clusters;
     auto slot_buf0 = [&](int slot) {  // lane 0's candidate buffer of this warp for that slot
-      return p.sink.cand + ((static_cast<int64_t>(blockIdx.x) * 2 + slot) * BLOCK_M + ew * 32) * cap;
+      return p.sink.cand + (((static_cast<int64_t>(blockIdx.x) * 2 + slot) * SETS + set) * BLOCK_M + ew * 32) * cap;
     };
     auto slot_qrow0 = [&](int slot) { return ((qt_base + slot) * CG + rank) * BLOCK_M + ew * 32; };
     auto slot_valid = [&](int slot) { return qt_base + slot < p.num_qt && slot_qrow0(slot) + lane < p.nq; };
@@ -324,6 +329,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         float tau_next = valid ? tau_load(p.sink.tau_g, qrow) : cur.tau;
 
         for (int64_t t = r0 + lo; t < r0 + hi; ++t, ++iter) {
+          if (SETS == 2 && (iter & 1u) != set) continue;  // the other set's accumulator buffer
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
           mbar_wait(&tfull[as], aph);
           tc_fence_after();
@@ -481,14 +487,14 @@ int make_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, int64_t l
   return NXF_OK;
 }
 
-template <int CG, bool BF16>
+template <int CG, bool BF16, int SETS>
 static int launch_k1_t(const CUtensorMap& tq, const CUtensorMap& tc, const K1Params& p, int grid, cudaStream_t stream) {
   using C = k1::Cfg<CG>;
-  auto kern = k1_search_kernel<CG, BF16>;
+  auto kern = k1_search_kernel<CG, BF16, SETS>;
   NXF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(static_cast<unsigned>(grid));
-  cfg.blockDim = dim3(k1::THREADS);
+  cfg.blockDim = dim3(128 + 128 * SETS);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -512,8 +518,12 @@ int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, 
   if (rc) return rc;
   rc = make_tmap_2d_sw128(&tc, corpus, p.n, ld, k1::BLOCK_N / cta_group, bf16);
   if (rc) return rc;
-  if (cta_group == 2) return bf16 ? launch_k1_t<2, true>(tq, tc, p, grid, stream) : launch_k1_t<2, false>(tq, tc, p, grid, stream);
-  return bf16 ? launch_k1_t<1, true>(tq, tc, p, grid, stream) : launch_k1_t<1, false>(tq, tc, p, grid, stream);
+  if (p.epi_sets == 2) {
+    if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 2>(tq, tc, p, grid, stream) : launch_k1_t<2, false, 2>(tq, tc, p, grid, stream);
+    return bf16 ? launch_k1_t<1, true, 2>(tq, tc, p, grid, stream) : launch_k1_t<1, false, 2>(tq, tc, p, grid, stream);
+  }
+  if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 1>(tq, tc, p, grid, stream) : launch_k1_t<2, false, 1>(tq, tc, p, grid, stream);
+  return bf16 ? launch_k1_t<1, true, 1>(tq, tc, p, grid, stream) : launch_k1_t<1, false, 1>(tq, tc, p, grid, stream);
 }
 
 int k1_smem_bytes(int cta_group) { return cta_group == 2 ? k1::Cfg<2>::SMEM_BYTES : k1::Cfg<1>::SMEM_BYTES; }
