@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--nq", type=int, default=0, help="override the number of queries")
     ap.add_argument("--n", type=int, default=0, help="override the number of corpus rows")
     ap.add_argument("--k", type=int, default=0)
+    ap.add_argument("--dim", type=int, default=0, help="override the embedding dimension (kernel experiments; the workload name says so)")
+    ap.add_argument("--store", default="", help="override the storage dtype (kernel experiments)")
     ap.add_argument("--flags", type=int, default=0, help="nxf_search flags (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -154,6 +156,9 @@ def run_reference(a):
     if rank != 0:
         return 0
     Q, N, D, k, store, norm, desc = CONFIGS[a.config]
+    if a.dim or a.store:
+        D, store = a.dim or D, a.store or store
+        desc += f" [override: dim {D}, store {store}]"
     Q, N, k = a.nq or Q, a.n or N, a.k or k
     rows = min(a.cpu_sample_rows, N)
     sq = min(a.cpu_sample_queries, Q)
@@ -216,6 +221,9 @@ def run_ours(a):
         dist.init_process_group("nccl", device_id=device)
 
     Q, N, D, k, store, norm, desc = CONFIGS[a.config]
+    if a.dim or a.store:
+        D, store = a.dim or D, a.store or store
+        desc += f" [override: dim {D}, store {store}]"
     Q, N, k = a.nq or Q, a.n or N, a.k or k
     lo, hi = shard_bounds(N, world)[rank]
     idx = FlatIndex(D, "ip", store, device=local_rank)

@@ -657,10 +657,14 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.chunks = static_cast<int>(ceil_div64(std::max<int64_t>(P.n_tiles, 1), P.round_tiles));  // reported as "chunks": rounds per launch
     // pruned between tiles once fewer than 256 (one tile of appends) slots are left
     P.cap = std::max(2, env_int("NXF_K1_CAP_MULT", 2)) * P.k_fetch + 256;
-    // a second epilogue warp set when a tile holds too few K blocks for one set to hide behind the MMAs (search_tc.cu); NXF_K1_SETS=1/2 overrides
+    // a second epilogue warp set when a tile holds too few K blocks for one set to hide behind the MMAs (search_tc.cu); NXF_K1_SETS=1/2
+    // overrides.  Measured (4 M rows, 16 384 queries, same box, one -> two sets): D = 64 +65 %, 128 +35 %, 256 +7 %, 320 +3 %, 384-512 +2 %,
+    // 768 and 1536 +-0
     {
       const int kb_tile = static_cast<int>(idx->ld / 64) * (P.split ? 3 : 1);
-      P.epi_sets = std::max(1, std::min(2, env_int("NXF_K1_SETS", kb_tile <= 6 ? 2 : 1)));
+      // small searches (C1: 21 tile-units per cluster) lose 7 % to the second set's fixed costs (twice the lists to flush and merge)
+      const int64_t units_per_cluster = static_cast<int64_t>(P.num_qt) * P.n_tiles / std::max(used, 1);
+      P.epi_sets = std::max(1, std::min(2, env_int("NXF_K1_SETS", (kb_tile <= 8 && units_per_cluster >= 128) ? 2 : 1)));
     }
     P.owners = static_cast<int64_t>(P.grid) * 128 * 2 * P.epi_sets;  // two query-tile slots per CTA, one buffer per (slot, set, row)
     // arena slice of a query: the list left by the sample passes (<= k' entries) + up to k' entries from every cluster that owns
