@@ -256,7 +256,8 @@ def test_sampled_thresholds_l2_metric(path, q):
 
 def test_tensor_kernel_multi_launch_batches():
     """More queries than one launch holds (148 SMs: 18 944): full launches and a shorter last one, whose query tiles are shared by more
-    clusters (longer arena slices).  Checked on queries from the first, the middle and the last launch."""
+    clusters (longer arena slices).  Checked on queries from the first, the middle and the last launch.  (Short rows on a long
+    search: the default picks K1's two epilogue sets here.)"""
     from nexus_b200 import FlatIndex
     n, d, q, k = 270000, 64, 19500, 20
     c, x = gen_inputs(n, d, q, seed=321)
@@ -391,3 +392,52 @@ def test_errors_are_loud():
         idx.search(np.zeros((1, 16), np.float32), 5000)
     with pytest.raises(Exception):
         idx.search(np.zeros((9, 16), np.float32), 2, flags=FLAGS["tensor"] | FLAGS["exact"])   # two forced paths
+
+
+@pytest.fixture
+def k1_sets(request):
+    """NXF_K1_SETS for the duration of one test (the library reads it per search)."""
+    import os
+    old = os.environ.get("NXF_K1_SETS")
+    os.environ["NXF_K1_SETS"] = str(request.param)
+    yield request.param
+    if old is None:
+        os.environ.pop("NXF_K1_SETS", None)
+    else:
+        os.environ["NXF_K1_SETS"] = old
+
+
+@pytest.mark.parametrize("k1_sets", [1, 2], indirect=True)
+@pytest.mark.parametrize("path", ["tensor", "tensor_1cta"])
+@pytest.mark.parametrize("store,case", [
+    ("bf16", (3000, 64, 37, 10)), ("f16", (5000, 128, 130, 100)), ("bf16", (20000, 384, 300, 10)), ("bf16", (9000, 512, 257, 100)),
+    ("bf16", (4096, 96, 20, 500)), ("f32", (6000, 64, 140, 20)),
+])
+def test_tensor_kernel_epilogue_sets(k1_sets, path, store, case):
+    """K1 with one and with two epilogue warp sets (the second set filters the other TMEM buffer into its own per-row lists; the
+    default picks it for short rows on long searches only, so small tests would never run it): same results either way."""
+    n, d, q, k = case
+    c, x = gen_inputs(n, d, q, seed=1300 + d)
+    run_and_check(c, x, k, store=store, path=path, rtol=1e-5, expect_path="tensor", min_recall=0.999)
+
+
+@pytest.mark.parametrize("k1_sets", [2], indirect=True)
+@pytest.mark.parametrize("store,case", [("bf16", (300000, 64, 300, 100)), ("f16", (300000, 64, 260, 1000)), ("bf16", (270000, 128, 700, 10))])
+def test_tensor_kernel_two_sets_sampled_thresholds(k1_sets, store, case):
+    """Two epilogue sets through the sampled-threshold schedule (estimate, two sample passes, main, verification, fall-back)."""
+    n, d, q, k = case
+    c, x = gen_inputs(n, d, q, seed=1400 + n % 59)
+    idx, D, I, rep, st = run_and_check(c, x, k, store=store, path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
+    assert st["kernel_launches"] >= 8
+
+
+@pytest.mark.parametrize("k1_sets", [2], indirect=True)
+def test_tensor_kernel_two_sets_fallback(k1_sets):
+    n, d, q, k = 300000, 64, 200, 100
+    rng = np.random.default_rng(6)
+    c = (0.05 * rng.standard_normal((n, d))).astype(np.float32)
+    x = rng.standard_normal((q, d)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    hot = np.flatnonzero((np.arange(n) // 256) % 16 == 0)      # every row that matters lies in a sample tile: the fall-back must run
+    c[hot] += x[rng.integers(0, q, size=hot.size)] * rng.uniform(0.5, 1.0, size=(hot.size, 1)).astype(np.float32)
+    run_and_check(c, x, k, store="bf16", path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
