@@ -597,7 +597,12 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     // measured (C5, D = 64): the two extra launches cost ~0.1 ms and pay for themselves from nq * k' ~ 800 on (NXF_K2T_SEED=0/1 overrides)
     {
       const int seed_env = env_int("NXF_K2T_SEED", -1);
-      P.seed = seed_env >= 0 ? seed_env != 0 : (nq * static_cast<int64_t>(P.k_fetch) >= 768);
+      // with the estimate-only first pass the sample launches cost ~25 us: on 128-byte rows they pay from nq * k' ~ 200 on (C5 corpus,
+      // 16 queries k = 10: 0.309 -> 0.238 ms; one query k = 500: 0.280 -> 0.237 ms; one query k = 10: 0.218 -> 0.232 ms, left alone);
+      // long rows amortise the appends over more stream bytes and keep the old threshold (C2, 2-4 queries: -1 % with the launches)
+      const int64_t row_bytes_k2t = idx->ld * static_cast<int64_t>(dtype_size(idx->store_dtype));
+      const int64_t seed_from = row_bytes_k2t < 512 ? 192 : 768;
+      P.seed = seed_env >= 0 ? seed_env != 0 : (nq * static_cast<int64_t>(P.k_fetch) >= seed_from);
     }
     P.arena_stride = static_cast<int64_t>(P.grid) * P.k_fetch;
     P.batch = std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ);
