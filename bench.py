@@ -202,7 +202,7 @@ def run_ours(a):
     import torch.distributed as dist
     from nexus_b200 import FlatIndex, merge_topk, shard_bounds
     from nexus_b200 import _lib as L
-    from nexus_b200.sharded import all_gather_lists
+    from nexus_b200.sharded import PARTITION_MIN_BYTES, all_gather_lists, exchange_partitioned
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -244,11 +244,22 @@ def run_ours(a):
     out_i = torch.empty((Q, k), dtype=torch.int64).pin_memory()
     flags = a.flags
 
+    # the one exchange step: all-gather of the per-shard [Q,k] lists + merge kernel; for large Q*k (C5: 393 MB per rank) the
+    # query-partitioned form (all-to-all by query block, merge, all-gather of the merged blocks: 2/world of the bytes)
+    partitioned = world > 2 and Q * k * 12 * world >= PARTITION_MIN_BYTES
+    if os.environ.get("NXF_BENCH_EXCHANGE") in ("gather", "partition"):        # A/B of the two exchanges
+        partitioned = world > 1 and os.environ["NXF_BENCH_EXCHANGE"] == "partition"
+
+    def exchange(D_, I_):
+        if partitioned:
+            return exchange_partitioned(D_, I_, world, k, "ip", None, merge_topk)
+        Ds, Is = all_gather_lists(D_, I_, world)
+        return merge_topk(Ds, Is, k)
+
     def step_dev():
         D_, I_ = idx.search(q, k, flags=flags)
         if world > 1:
-            Ds, Is = all_gather_lists(D_, I_, world)
-            D_, I_ = merge_topk(Ds, Is, k)
+            D_, I_ = exchange(D_, I_)
         return D_, I_
 
     def step_e2e():
@@ -256,8 +267,7 @@ def run_ours(a):
             return idx.search(q_host, k, flags=flags, out=(out_d, out_i))     # host buffers through the C ABI
         qd = q_host.to(device, non_blocking=True)
         D_, I_ = idx.search(qd, k, flags=flags)
-        Ds, Is = all_gather_lists(D_, I_, world)
-        D_, I_ = merge_topk(Ds, Is, k)
+        D_, I_ = exchange(D_, I_)
         if rank == 0:
             out_d.copy_(D_, non_blocking=True)
             out_i.copy_(I_, non_blocking=True)
@@ -370,7 +380,8 @@ def run_ours(a):
         "data": "synthetic",
         "config": {"workload": desc, "nq": Q, "n": N, "dim": D, "k": k, "store_dtype": store, "path": path,
                    "k_fetch": st1["last_k_fetch"], "chunks": st1["last_chunks"], "grid": st1["last_grid"],
-                   "parallelism": f"corpus rows sharded x{world}" + (", NCCL all-gather of per-shard top-k + merge kernel" if world > 1 else ""),
+                   "parallelism": f"corpus rows sharded x{world}" + ((", NCCL all-to-all of per-shard top-k by query block + merge kernel + all-gather of the merged blocks" if partitioned
+                                                                          else ", NCCL all-gather of per-shard top-k + merge kernel") if world > 1 else ""),
                    "l2_policy": "inputs larger than L2 (corpus shard %.1f GB vs 126 MB L2); no flush needed" % ((hi - lo) * D * (4 if store == "f32" else 2) / 1e9),
                    "index_build_s": t_build},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "check": check,

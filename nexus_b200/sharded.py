@@ -172,12 +172,56 @@ class DistributedFlatIndex:
         self.local.reset()
         self._ntotal_global = 0
 
-    def search(self, q, k: int, gather=None, merge=None):
+    def search(self, q, k: int, gather=None, merge=None, exchange: str = "auto"):
         """``q``: the same [Q, D] CUDA tensor on every rank.  Returns the merged ``(D, I)`` on every rank.
+        ``exchange``: ``"gather"`` = one all-gather of the per-shard ``[Q, k]`` lists + merge on every rank (the north star's form);
+        ``"partition"`` = rank r receives only the lists of its own block of queries (all-to-all), merges them and the final blocks
+        are all-gathered -- 2/world of the bytes, for large ``Q*k``; ``"auto"`` picks by size.
         ``gather`` / ``merge`` are injection points for the CPU (gloo) tests of the exchange logic."""
         D, I = self.local.search(q, int(k))
+        metric = "l2" if self._metric == "l2" else "ip"
+        if exchange == "auto":
+            exchange = "partition" if (self.world > 2 and D.numel() * 12 * self.world >= PARTITION_MIN_BYTES and gather is None) else "gather"
+        if exchange == "partition":
+            return exchange_partitioned(D, I, self.world, int(k), metric, self.group, merge or merge_topk)
         Ds, Is = (gather or all_gather_lists)(D, I, self.world, self.group)
-        return (merge or merge_topk)(Ds, Is, int(k), "l2" if self._metric == "l2" else "ip")
+        return (merge or merge_topk)(Ds, Is, int(k), metric)
+
+
+# all-gather volume (bytes received per rank) from which the query-partitioned exchange is used: below, one collective wins
+PARTITION_MIN_BYTES = 256 << 20
+
+
+def exchange_partitioned(D, I, world: int, k: int, metric: str = "ip", group=None, merge=None):
+    """Query-partitioned exchange of per-shard top-k lists: ``[Q, k]`` on every rank -> merged ``[Q, k]`` on every rank.
+    Queries are cut into ``world`` equal blocks (the last one padded with empty lists); one all-to-all hands rank r every shard's
+    lists of block r, rank r merges them (``merge(Ds [world, Qb, k], Is, k, metric)``), one all-gather distributes the merged
+    blocks.  Bytes received per rank: 2 * Q*k*12 * (world-1)/world instead of Q*k*12 * (world-1)."""
+    import torch
+    import torch.distributed as dist
+    merge = merge or merge_topk
+    Q = int(D.shape[0])
+    Qb = (Q + world - 1) // world
+    if Qb * world != Q:
+        pad = Qb * world - Q
+        fill = float(np.finfo(np.float32).max) if metric == "l2" else -float(np.finfo(np.float32).max)
+        D = torch.cat([D, torch.full((pad, k), fill, dtype=D.dtype, device=D.device)], 0)
+        I = torch.cat([I, torch.full((pad, k), -1, dtype=I.dtype, device=I.device)], 0)
+    D, I = D.contiguous(), I.contiguous()
+    Dr, Ir = torch.empty_like(D), torch.empty_like(I)
+    dist.all_to_all_single(Dr, D, group=group)            # Dr[g*Qb:(g+1)*Qb] = shard g's lists for my query block
+    dist.all_to_all_single(Ir, I, group=group)
+    Dm, Im = merge(Dr.view(world, Qb, k), Ir.view(world, Qb, k), k, metric)
+    Dm, Im = Dm.contiguous(), Im.contiguous()
+    Do = torch.empty((world * Qb, k), dtype=Dm.dtype, device=Dm.device)
+    Io = torch.empty((world * Qb, k), dtype=Im.dtype, device=Im.device)
+    if hasattr(dist, "all_gather_into_tensor") and Dm.is_cuda:
+        dist.all_gather_into_tensor(Do, Dm, group=group)
+        dist.all_gather_into_tensor(Io, Im, group=group)
+    else:
+        dist.all_gather(list(Do.view(world, Qb, k).unbind(0)), Dm, group=group)
+        dist.all_gather(list(Io.view(world, Qb, k).unbind(0)), Im, group=group)
+    return Do[:Q], Io[:Q]
 
 
 def all_gather_lists(D, I, world: int, group=None):
