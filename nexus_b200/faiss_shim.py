@@ -175,9 +175,48 @@ def write_index(index, path: str) -> None:
         rows.astype(np.float32).tofile(f)
 
 
+def _read_faiss_flat(f, fourcc: bytes):
+    """Native Faiss flat index file ('IxFI' = IndexFlatIP, 'IxF2' = IndexFlatL2, 'IxFl' = old IndexFlat), restated from Faiss's
+    published writer (faiss/impl/index_write.cpp: write_index_header + the flat payload): int32 d, int64 ntotal, 2 x int64 dummy,
+    uint8 is_trained, int32 metric_type (+ float32 metric_arg when metric_type > 1), uint64 count, count x float32 row-major.
+    PARITY UNPINNED: Faiss is not installable in this image, so no real file was available to check this against."""
+    import struct
+    d, = struct.unpack("<i", f.read(4))
+    ntotal, _d1, _d2 = struct.unpack("<qqq", f.read(24))
+    _trained, = struct.unpack("<B", f.read(1))
+    metric, = struct.unpack("<i", f.read(4))
+    if metric > 1:
+        f.read(4)
+    count, = struct.unpack("<Q", f.read(8))
+    if d <= 0 or ntotal < 0 or count != ntotal * d:
+        raise ValueError(f"read_index: inconsistent Faiss flat header (d={d}, ntotal={ntotal}, payload={count} floats)")
+    if metric not in (METRIC_INNER_PRODUCT, METRIC_L2):
+        raise ValueError(f"read_index: Faiss metric_type {metric} is not served (inner product and L2 only)")
+    if fourcc == b"IxFI":
+        metric = METRIC_INNER_PRODUCT
+    elif fourcc == b"IxF2":
+        metric = METRIC_L2
+    rows = np.fromfile(f, dtype="<f4", count=int(count)).reshape(int(ntotal), int(d))
+    if rows.shape[0] != ntotal:
+        raise ValueError("read_index: truncated Faiss flat file")
+    return int(d), int(metric), rows
+
+
+def write_index_faiss_flat(index, path: str) -> None:
+    """The same rows in Faiss's native flat layout (see :func:`_read_faiss_flat`), for files that real Faiss should open."""
+    import struct
+    rows = index.reconstruct_n() if index.ntotal else np.empty((0, index.d), np.float32)
+    with open(path, "wb") as f:
+        f.write(b"IxFI" if index.metric_type == METRIC_INNER_PRODUCT else b"IxF2")
+        f.write(struct.pack("<iqqqBi", int(index.d), int(rows.shape[0]), 1 << 20, 1 << 20, 1, int(index.metric_type)))
+        f.write(struct.pack("<Q", int(rows.size)))
+        np.ascontiguousarray(rows, dtype="<f4").tofile(f)
+
+
 def read_index(path: str):
-    """Reads files written by :func:`write_index`, and ``.npy`` embedding caches (doc.npy / corpus_embeddings.npy,
-    searcher.py:126-127,144) as inner-product indices."""
+    """Reads files written by :func:`write_index`, ``.npy`` embedding caches (doc.npy / corpus_embeddings.npy,
+    searcher.py:126-127,144) as inner-product indices, and native Faiss FLAT index files (serve/inference_service_text_retrieval.py:35
+    reads whatever ``faiss.write_index`` produced; other Faiss index types need Faiss itself)."""
     with open(path, "rb") as f:
         head = f.read(8)
         if head == _MAGIC:
@@ -187,13 +226,20 @@ def read_index(path: str):
             if n:
                 idx.add(rows)
             return idx
+        if head[:4] in (b"IxFI", b"IxF2", b"IxFl"):
+            f.seek(4)
+            d, metric, rows = _read_faiss_flat(f, head[:4])
+            idx = _LazyFlat(d, metric)
+            if rows.shape[0]:
+                idx.add(rows)
+            return idx
     if head[:6] == b"\x93NUMPY":
         rows = np.load(path, mmap_mode="r")
         idx = _LazyFlat(int(rows.shape[1]), METRIC_INNER_PRODUCT)
         idx.add(np.ascontiguousarray(rows))
         return idx
-    raise ValueError(f"read_index: {path} is neither a nexus_b200 flat index nor a .npy embedding cache "
-                     "(native Faiss files are not readable without Faiss)")
+    raise ValueError(f"read_index: {path} is neither a nexus_b200 flat index, a Faiss flat index, nor a .npy embedding cache "
+                     "(other native Faiss index types are not readable without Faiss)")
 
 
 def load_embedding_cache(path: str):

@@ -84,3 +84,22 @@ def test_recsys_item_index_flow_from_item_vectors_pt(tmp_path):
     idx2, ids2 = F.index_from_cache(str(tmp_path / "item_vectors.pt"))
     D2, I2 = idx2.search(users, 50)
     np.testing.assert_array_equal(I2, I)
+
+
+def test_read_index_of_a_faiss_native_flat_file(tmp_path):
+    """serve/inference_service_text_retrieval.py:35,70: faiss.read_index(path) at import, index.search(q[None, :], k=20) per request --
+    on a file in Faiss's native flat layout (written here by write_index_faiss_flat; parity of the layout itself is unpinned)."""
+    from nexus_b200 import faiss_shim as F
+    rng = np.random.default_rng(33)
+    docs = rng.standard_normal((3000, 384)).astype(np.float32)
+    docs /= np.linalg.norm(docs, axis=1, keepdims=True)
+    index = F.IndexFlatIP(384)
+    index.add(docs)
+    F.write_index_faiss_flat(index, str(tmp_path / "doc.index"))
+    served = F.read_index(str(tmp_path / "doc.index"))
+    assert served.ntotal == 3000 and served.d == 384
+    q = rng.standard_normal(384).astype(np.float32)
+    D, I = served.search(q[None, :], 20)
+    ref_s, ref_i = oracle.blocked_ip_search(docs, q[None, :], 20)
+    rep = oracle.check_topk(ref_s, ref_i, D, I, docs, q[None, :], rtol=1e-5)
+    assert rep.ok, rep.messages[:5]

@@ -165,3 +165,36 @@ def test_ivfflat_constructor_shape():
     index.nprobe = 10                      # recommendation/base.py:117: settable, ignored
     index.train(np.zeros((4, 32), np.float32))
     assert F.IndexIVFFlat(quantizer, 32, 100).metric_type == F.METRIC_L2   # Faiss's default metric for this class
+
+
+def test_faiss_native_flat_file_layout(tmp_path):
+    """Faiss's own flat file layout (index_write.cpp, restated; unpinned -- no Faiss in this image): header parse, payload,
+    truncation and inconsistent headers are loud.  No device is touched: the parser is called directly."""
+    import struct
+    from nexus_b200 import faiss_shim as F
+    rows = np.arange(15, dtype=np.float32).reshape(5, 3)
+
+    class Fake:
+        d, metric_type, ntotal = 3, F.METRIC_INNER_PRODUCT, 5
+        def reconstruct_n(self):
+            return rows
+    p = tmp_path / "flat.index"
+    F.write_index_faiss_flat(Fake(), str(p))
+    raw = open(p, "rb").read()
+    assert raw[:4] == b"IxFI" and len(raw) == 4 + 4 + 24 + 1 + 4 + 8 + 60
+    with open(p, "rb") as f:
+        f.seek(4)
+        d, metric, got = F._read_faiss_flat(f, b"IxFI")
+    assert (d, metric) == (3, F.METRIC_INNER_PRODUCT) and np.array_equal(got, rows)
+    bad = tmp_path / "bad.index"                       # payload count does not match ntotal * d
+    bad.write_bytes(raw[:37] + struct.pack("<Q", 14) + raw[45:])
+    with open(bad, "rb") as f:
+        f.seek(4)
+        with pytest.raises(ValueError):
+            F._read_faiss_flat(f, b"IxFI")
+    trunc = tmp_path / "trunc.index"
+    trunc.write_bytes(raw[:-8])
+    with open(trunc, "rb") as f:
+        f.seek(4)
+        with pytest.raises(ValueError):
+            F._read_faiss_flat(f, b"IxFI")
