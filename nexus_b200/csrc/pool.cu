@@ -11,6 +11,10 @@
 // entirely (the reference multiplies them by 0) and splits L over thread groups.
 #include <algorithm>
 #include <climits>
+#include <cstdlib>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "common.cuh"
 
@@ -18,6 +22,9 @@ namespace nxf {
 
 #ifndef NXF_POOL_CTAS
 #define NXF_POOL_CTAS (6 * 3 * 148)
+#endif
+#ifndef NXF_POOL_WS_CACHE_DEFAULT
+#define NXF_POOL_WS_CACHE_DEFAULT 0   // 1: the split kernel's workspace is cached per (device, stream) (NXF_POOL_WS_CACHE overrides)
 #endif
 #ifndef NXF_POOL_UNROLL
 #define NXF_POOL_UNROLL 8
@@ -291,7 +298,38 @@ __global__ void __launch_bounds__(512) pool_mean_split_kernel(const T* __restric
   }
   O* ob = out + b * H;
   for (int64_t h = tid; h < H; h += nthr) ob[h] = from_f32<O>(normalize ? vals[h] * scale : vals[h]);
+  // leave the row's control words as they were found (zero): the workspace is cached per (device, stream) and the next launch on
+  // the stream starts without a memset.  Nobody else touches them any more: every CTA of the row has already arrived.
+  __syncthreads();  // every thread of this (last) CTA has read den_g[b] by now
+  if (tid == 0) { den_g[b] = 0ull; counter[b] = 0u; }
 }
+
+// Workspace of the split kernel, cached per (device, stream): [control words of up to 65 535 rows (den u64 | counter u32), zero
+// between launches][fp32 partial sums].  Launches on one stream are ordered, so they can share it; other streams get their own.
+// (cudaMallocAsync + memset + cudaFreeAsync per call were a third of the host time of a default encode batch's pooling call.)
+namespace {
+struct PoolWs { unsigned char* p = nullptr; size_t bytes = 0; };
+constexpr size_t kPoolCtlBytes = size_t(65536) * 16;
+std::mutex g_pool_mu;
+std::map<std::pair<int, cudaStream_t>, PoolWs> g_pool_ws;
+
+int pool_workspace(size_t part_bytes, cudaStream_t stream, unsigned char** out) {
+  int dev = 0;
+  NXF_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_pool_mu);
+  PoolWs& w = g_pool_ws[{dev, stream}];
+  const size_t want = kPoolCtlBytes + part_bytes;
+  if (w.bytes < want) {
+    if (w.p) { NXF_CUDA(cudaStreamSynchronize(stream)); cudaFree(w.p); w.p = nullptr; w.bytes = 0; }
+    const size_t alloc = (want + (size_t(4) << 20)) & ~((size_t(1) << 20) - 1);
+    NXF_CUDA(cudaMalloc(reinterpret_cast<void**>(&w.p), alloc));
+    w.bytes = alloc;
+    NXF_CUDA(cudaMemsetAsync(w.p, 0, kPoolCtlBytes, stream));
+  }
+  *out = w.p;
+  return NXF_OK;
+}
+}  // namespace
 
 template <typename T, typename O, int VEC>
 static int launch_pool_mean_split(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int normalize, float eps,
@@ -303,20 +341,33 @@ static int launch_pool_mean_split(const void* hidden, const int64_t* mask, int64
   int splits = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>((NXF_POOL_CTAS + B - 1) / B, std::max<int64_t>(1, L / 64))));
   const size_t smem = static_cast<size_t>(G) * H * 4;
   const size_t part_bytes = static_cast<size_t>(B) * splits * H * 4;
-  const size_t ctl_bytes = static_cast<size_t>(B) * 16;  // den (u64) + counter (u32), 16 bytes per row
+  auto kern = pool_mean_split_kernel<T, O, VEC>;
+  if (smem > 48 * 1024) NXF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  const char* ws_env = getenv("NXF_POOL_WS_CACHE");  // read per call
+  const bool cached_ws = ws_env ? atoi(ws_env) != 0 : NXF_POOL_WS_CACHE_DEFAULT != 0;
+  if (cached_ws) {
+    unsigned char* ws = nullptr;
+    int rc = pool_workspace(part_bytes, stream, &ws);
+    if (rc) return rc;
+    unsigned long long* den = reinterpret_cast<unsigned long long*>(ws);
+    unsigned int* counter = reinterpret_cast<unsigned int*>(ws + size_t(65536) * 8);
+    float* partial = reinterpret_cast<float*>(ws + kPoolCtlBytes);
+    kern<<<dim3(static_cast<unsigned>(splits), static_cast<unsigned>(B)), threads, smem, stream>>>(
+        (const T*)hidden, mask, L, H, normalize, eps, (O*)out, G, partial, den, counter);
+    NXF_CUDA(cudaGetLastError());
+    return NXF_OK;
+  }
+  // stream-ordered allocation per call: partials | den (u64 per row) | counter (u32 per row), control words zeroed by a memset
+  const size_t ctl_bytes = static_cast<size_t>(B) * 16;
   unsigned char* ws = nullptr;
   NXF_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&ws), part_bytes + ctl_bytes, stream));
   unsigned long long* den = reinterpret_cast<unsigned long long*>(ws + part_bytes);
   unsigned int* counter = reinterpret_cast<unsigned int*>(ws + part_bytes + static_cast<size_t>(B) * 8);
   cudaError_t e = cudaMemsetAsync(ws + part_bytes, 0, ctl_bytes, stream);
   if (e == cudaSuccess) {
-    auto kern = pool_mean_split_kernel<T, O, VEC>;
-    if (smem > 48 * 1024) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-    if (e == cudaSuccess) {
-      kern<<<dim3(static_cast<unsigned>(splits), static_cast<unsigned>(B)), threads, smem, stream>>>(
-          (const T*)hidden, mask, L, H, normalize, eps, (O*)out, G, reinterpret_cast<float*>(ws), den, counter);
-      e = cudaGetLastError();
-    }
+    kern<<<dim3(static_cast<unsigned>(splits), static_cast<unsigned>(B)), threads, smem, stream>>>(
+        (const T*)hidden, mask, L, H, normalize, eps, (O*)out, G, reinterpret_cast<float*>(ws), den, counter);
+    e = cudaGetLastError();
   }
   cudaFreeAsync(ws, stream);
   NXF_CUDA(e);

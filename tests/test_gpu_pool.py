@@ -76,3 +76,31 @@ def test_encode_to_index_handoff_stays_on_device():
     D, I = idx.search(emb[:64], 1)
     assert (I[:, 0].cpu() == torch.arange(64)).all()                       # every row's nearest neighbour is itself
     assert torch.allclose(D[:, 0].cpu(), torch.ones(64), atol=2e-2)
+
+
+@pytest.mark.parametrize("cache", ["0", "1"])
+def test_mean_pool_workspace_reuse_across_shapes_and_streams(cache, monkeypatch):
+    """NXF_POOL_WS_CACHE=1: the split mean kernel's workspace is cached per (device, stream) and its control words must be back at
+    zero after every launch: repeated calls, growing / shrinking batch sizes, and a second stream all give the oracle's result
+    (=0: one stream-ordered allocation per call)."""
+    import torch
+    monkeypatch.setenv("NXF_POOL_WS_CACHE", cache)
+    import oracle
+    from nexus_b200 import pool_and_normalize
+    gen = torch.Generator().manual_seed(9)
+    side = torch.cuda.Stream()
+    for rep, (B, Lq, H) in enumerate([(4, 256, 384), (64, 512, 768), (3, 1024, 128), (64, 512, 768), (130, 64, 256), (4, 256, 384)]):
+        h = torch.randn(B, Lq, H, generator=gen).half()
+        lens = torch.randint(1, Lq + 1, (B, 1), generator=gen)
+        m = (torch.arange(Lq)[None, :] < lens).long()
+        ref = oracle.pool_and_normalize(h.float().numpy(), m.numpy(), "mean", normalize=True)
+        hd, md = h.cuda(), m.cuda()
+        for _ in range(3):
+            out = pool_and_normalize(hd, md, "mean", normalize=True)
+            np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=2e-5, atol=2e-6)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            out2 = pool_and_normalize(hd, md, "mean", normalize=rep % 2 == 0)
+        side.synchronize()
+        ref2 = ref if rep % 2 == 0 else oracle.pool_and_normalize(h.float().numpy(), m.numpy(), "mean", normalize=False)
+        np.testing.assert_allclose(out2.cpu().numpy(), ref2, rtol=2e-5, atol=2e-6)
