@@ -130,6 +130,29 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
+def probe_faiss_cpu(sample_rows, sample_q, d, k, n_full, normalised):
+    """if a REAL faiss is importable on this box, time IndexFlatIP exactly as the reference calls it (32-row
+    query chunks, utils.py:221-224) on the same bounded sample; otherwise say so.  Never our own shim."""
+    try:
+        import faiss
+        if getattr(faiss, "__nexus_b200__", False) or not hasattr(faiss, "IndexFlatIP"):
+            raise ImportError("only the nexus_b200 shim is registered as faiss")
+    except Exception as e:  # noqa: BLE001
+        return {"available": False, "note": f"Faiss CPU: unavailable on this box ({type(e).__name__})"}
+    import numpy as np
+    import oracle
+    c = oracle.round_to_bf16(oracle.make_unit_gaussian(sample_rows, d, seed=1002, normalize=normalised))
+    q = oracle.make_unit_gaussian(sample_q, d, seed=2002, normalize=normalised)
+    index = faiss.index_factory(d, "Flat", faiss.METRIC_INNER_PRODUCT)
+    index.add(c)
+    t0 = time.perf_counter()
+    for i in range(0, sample_q, 32):
+        index.search(np.ascontiguousarray(q[i:i + 32], dtype=np.float32), k)
+    t = time.perf_counter() - t0
+    return {"available": True, "value": sample_q / (t * (n_full / float(sample_rows))), "unit": "queries/s", "seconds": t,
+            "call": "IndexFlatIP.search, 32-row chunks (utils.py:221-224)"}
+
+
 def cpu_reference_search(sample_rows, sample_q, d, k, n_full, normalised, steps=1, warmup=0):
     """Times the oracle port of the reference CPU search (NumpyIPIndex math, blocked) on a bounded sample and
     scales linearly in N to the full corpus: value = Q_s / (t * N / N_s).  Returns (qps, seconds per step, cores)."""
@@ -171,7 +194,8 @@ def run_reference(a):
         "config": {"workload": desc, "nq": Q, "n": N, "dim": D, "k": k,
                    "note": "faiss is not installable offline; this is the oracle port of the reference's own NumpyIPIndex/search "
                            "(Nexus/evaluation/text_retrieval/utils.py:16-31,194-230), blocked so that it fits in RAM"},
-        "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port", "sample": sample,
+                         "faiss_cpu": probe_faiss_cpu(rows, sq, D, k, N, norm)},
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -372,7 +396,8 @@ def run_ours(a):
         rows, sq = min(a.cpu_sample_rows, N), min(a.cpu_sample_queries, Q)
         qps, t, cores = cpu_reference_search(rows, sq, D, k, N, norm)
         cpu = {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port", "seconds": t,
-               "sample": f"{sq} queries x {rows} rows x {D} (of {Q} x {N}); queries/s scaled linearly in N"}
+               "sample": f"{sq} queries x {rows} rows x {D} (of {Q} x {N}); queries/s scaled linearly in N",
+               "faiss_cpu": probe_faiss_cpu(rows, sq, D, k, N, norm)}
 
     line = {
         "metric": "queries/sec exact top-k flat search", "value": value, "unit": "queries/s", "n_gpus": world, "steps": a.steps,
