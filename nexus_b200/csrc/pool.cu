@@ -24,7 +24,7 @@ namespace nxf {
 #define NXF_POOL_CTAS (6 * 3 * 148)
 #endif
 #ifndef NXF_POOL_WS_CACHE_DEFAULT
-#define NXF_POOL_WS_CACHE_DEFAULT 0   // 1: the split kernel's workspace is cached per (device, stream) (NXF_POOL_WS_CACHE overrides)
+#define NXF_POOL_WS_CACHE_DEFAULT 1   // 1: the split kernel's workspace is cached per (device, stream) (NXF_POOL_WS_CACHE overrides)
 #endif
 #ifndef NXF_POOL_UNROLL
 #define NXF_POOL_UNROLL 8
