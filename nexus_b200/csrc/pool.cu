@@ -26,8 +26,11 @@ namespace nxf {
 #ifndef NXF_POOL_WS_CACHE_DEFAULT
 #define NXF_POOL_WS_CACHE_DEFAULT 1   // 1: the split kernel's workspace is cached per (device, stream) (NXF_POOL_WS_CACHE overrides)
 #endif
+#ifndef NXF_POOL_MINB
+#define NXF_POOL_MINB 3   // min resident CTAs per SM asked of the split kernel (register cap: 54 -> 40 registers, 2 -> 3 CTAs of 480 threads)
+#endif
 #ifndef NXF_POOL_UNROLL
-#define NXF_POOL_UNROLL 8
+#define NXF_POOL_UNROLL 4
 #endif
 namespace k0 {
 constexpr int MEAN_UNROLL = NXF_POOL_UNROLL;
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(k0::THREADS) pool_norm_kernel(const T* __restr
 // row) adds the partials in a fixed order -- results do not depend on the arrival order --, divides by the mask sum,
 // normalises, casts and stores.
 template <typename T, typename O, int VEC>
-__global__ void __launch_bounds__(512) pool_mean_split_kernel(const T* __restrict__ hidden, const int64_t* __restrict__ mask, int64_t L,
+__global__ void __launch_bounds__(512, NXF_POOL_MINB) pool_mean_split_kernel(const T* __restrict__ hidden, const int64_t* __restrict__ mask, int64_t L,
                                                               int64_t H, int normalize, float eps, O* __restrict__ out, int G,
                                                               float* __restrict__ partial, unsigned long long* __restrict__ den_g,
                                                               unsigned int* __restrict__ counter) {
