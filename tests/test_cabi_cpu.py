@@ -109,3 +109,31 @@ def test_sample_rank_bounds_the_failure_probability(lib, k, s, n):
         rows = 256
         assert stats.hypergeom.logsf(m - 1, n * rows, k, s * rows) <= -30.0
     assert lib.nxf_sample_rank(0, s, n) < 0 and lib.nxf_sample_rank(k, n + 1, n) < 0
+
+
+def test_header_is_plain_c_and_a_c_program_links(tmp_path):
+    """The boundary is a C ABI: include/nexus_flat.h must compile as C (no C++ in the signatures) and a C program must link
+    against the shared library and run its host-only entry points without a GPU."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("gcc not found")
+    from nexus_b200 import _lib as L
+    inc = os.path.join(ROOT, "include")
+    src = tmp_path / "probe.c"
+    src.write_text(
+        '#include <stdio.h>\n#include "nexus_flat.h"\n'
+        "int main(void) {\n"
+        "  nxf_index* idx = 0;\n"
+        '  printf("%s\\n", nxf_version());\n'
+        "  int m = nxf_sample_rank(128, 1000, 16000);\n"
+        "  int rc = nxf_search_subsets(idx, 0, 1, NXF_F32, 0, 0, 0, 0, 0, 0, 10, 0, 0, 0, 0);\n"   # NULL index: NXF_EINVAL
+        '  printf("%d %d %d\\n", m, rc, (int)nxf_ntotal(idx));\n'
+        "  return (m >= 1 && m <= 128 && rc == NXF_EINVAL) ? 0 : 1;\n}\n")
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Werror", "-pedantic", "-fsyntax-only", "-I", inc, str(src)], check=True)
+    exe = tmp_path / "probe"
+    subprocess.run([gcc, "-std=c99", "-I", inc, str(src), "-o", str(exe), L.LIB_PATH, "-Wl,-rpath," + os.path.dirname(L.LIB_PATH)], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    assert r.stdout.startswith("nexus_flat ")
