@@ -40,8 +40,14 @@
  *     id -1 and score -FLT_MAX (IP) / +FLT_MAX (L2) -- the padding searcher.py:156 already skips.
  *   - Row ids are insertion order, 0-based, int64, plus the index's id offset (nxf_set_id_offset),
  *     which is how a row shard reports global ids.
- *   - Thread-safety: one handle may be used from several threads; add/reset/search on the SAME
- *     handle are serialised internally (the reference is single-threaded at this seam).
+ *   - Thread-safety and streams: one handle may be used from several threads and on several streams.
+ *     Calls on the SAME handle are serialised on the host (a mutex) AND on the device: the handle's
+ *     scratch arena, staging buffers and row storage are shared, so a call issued on a stream other
+ *     than the previous call's first makes its stream wait (cudaStreamWaitEvent) for the device work
+ *     the previous call enqueued.  Searches on two streams therefore return correct results without
+ *     any caller-side synchronisation, but they run one after the other on the device (every search
+ *     kernel fills the GPU; the reference is single-threaded at this seam).  Distinct handles share
+ *     nothing and overlap freely.
  */
 #ifndef NEXUS_FLAT_H_
 #define NEXUS_FLAT_H_
@@ -194,6 +200,24 @@ NXF_API int nxf_search_subsets(nxf_index* idx, const void* q, int64_t nq, int q_
 NXF_API int nxf_merge_topk(const float* scores, const int64_t* ids, int n_lists, int64_t nq, int k,
                            int k_out, int metric, float* out_scores, int64_t* out_ids, int device,
                            void* stream);
+
+/* ---- row-sharded search: packed per-shard lists (device pointers only) ----
+ * What one shard contributes to the multi-GPU search that replaces faiss.index_cpu_to_all_gpus(index, co) with
+ * co.shard = True (Nexus/evaluation/text_retrieval/utils.py:178-183; Faiss merges IndexShards results on the host):
+ * nxf_search_packed is nxf_search with device queries whose result rows are written as [nq, k] 8-byte entries
+ * (float32 score, int32 SHARD-LOCAL row; row -1 = padding, score as in nxf_search) -- one buffer, so the per-shard lists
+ * travel in ONE all-gather of 8 bytes per entry (instead of float32 scores + int64 ids = 12 bytes in two collectives).
+ * nxf_merge_packed merges n_lists such lists ([n_lists, nq, k], rows best-first) into [nq, k_out] float32 scores and
+ * int64 GLOBAL ids: id = row + list_offsets[list] (list_offsets: HOST array of n_lists int64, the first global row of
+ * every shard).  n_lists <= 64.  Ties between lists are ordered by ascending global id, like nxf_merge_topk. */
+typedef struct nxf_entry {
+  float score;
+  int32_t row;
+} nxf_entry;
+NXF_API int nxf_search_packed(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int k, nxf_entry* out,
+                              int flags, void* stream);
+NXF_API int nxf_merge_packed(const nxf_entry* lists, const int64_t* list_offsets, int n_lists, int64_t nq, int k, int k_out,
+                             int metric, float* out_scores, int64_t* out_ids, int device, void* stream);
 
 /* ---- rank of the positive among the top-k (device pointers only) ----
  * Replaces torch.cat([pos_scores, topk_scores]) + stable torch.sort(descending) + `indice[:, :k] == 0` in

@@ -5,10 +5,10 @@ and the host-side mirror of the reference interface (``index``/``search``, a Fai
 pool+normalise, row-sharded multi-GPU search).  There is no CPU fallback anywhere in this package.
 """
 from ._lib import NexusFlatError, version  # noqa: F401
-from .flat import FlatIndex, merge_topk, positive_rank  # noqa: F401
+from .flat import FlatIndex, merge_packed, merge_topk, positive_rank  # noqa: F401
 from .sharded import DistributedFlatIndex, ShardedFlatIndex, shard_bounds  # noqa: F401
 from .retrieval import index, search, unpack_results  # noqa: F401
 from .pooling import pool_and_normalize, pooling  # noqa: F401
 
 __all__ = ["positive_rank", "unpack_results", "FlatIndex", "ShardedFlatIndex", "DistributedFlatIndex", "index", "search", "pool_and_normalize", "pooling",
-           "merge_topk", "shard_bounds", "NexusFlatError", "version"]
+           "merge_topk", "merge_packed", "shard_bounds", "NexusFlatError", "version"]

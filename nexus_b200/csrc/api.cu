@@ -7,6 +7,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <unordered_map>
 #include <thread>
 #include <vector>
 
@@ -31,6 +32,21 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
   if (e == cudaErrorMemoryAllocation) return NXF_ENOMEM;
   if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver || e == cudaErrorInvalidDevice) return NXF_ENODEVICE;
   return NXF_ECUDA;
+}
+
+int ensure_dyn_smem(const void* kernel, int bytes) {
+  struct Lim { int v[32]; };
+  static std::mutex mu;
+  static std::unordered_map<const void*, Lim> seen;
+  int dev = 0;
+  NXF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 32) { NXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); return NXF_OK; }
+  std::lock_guard<std::mutex> lk(mu);
+  Lim& l = seen[kernel];  // value-initialised to zeros
+  if (l.v[dev] >= bytes) return NXF_OK;
+  NXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  l.v[dev] = bytes;
+  return NXF_OK;
 }
 
 }  // namespace nxf
@@ -62,6 +78,12 @@ struct nxf_index {
   nxf_stats stats{};
   bool profiling = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;  // pending (start, stop) pairs
+  // Stream ordering between calls.  The scratch arena, the staging buffers and (add / reconstruct) the row storage are shared by
+  // every call on the handle, and device-in / device-out calls return before their kernels ran: each call records `last_use` on its
+  // stream when it has enqueued its work, and a call on a DIFFERENT stream first makes that stream wait for it (UseScope below).
+  cudaEvent_t last_use = nullptr;
+  cudaStream_t last_stream = nullptr;
+  bool used = false;
   std::mutex mu;
 };
 
@@ -76,6 +98,20 @@ struct DeviceGuard {
   }
   ~DeviceGuard() {
     if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// RAII: on entry the call's stream waits for the previous call on this handle if that ran on another stream; on exit (every
+// return path) the event is re-recorded behind whatever this call enqueued.  Constructed under idx->mu with the device current.
+struct UseScope {
+  nxf_index* idx;
+  cudaStream_t stream;
+  UseScope(nxf_index* i, cudaStream_t s) : idx(i), stream(s) {
+    if (idx->used && idx->last_stream != stream && idx->last_use) cudaStreamWaitEvent(stream, idx->last_use, 0);
+  }
+  ~UseScope() {
+    if (!idx->last_use && cudaEventCreateWithFlags(&idx->last_use, cudaEventDisableTiming) != cudaSuccess) { idx->last_use = nullptr; return; }
+    if (cudaEventRecord(idx->last_use, stream) == cudaSuccess) { idx->last_stream = stream; idx->used = true; }
   }
 };
 
@@ -289,6 +325,8 @@ void nxf_destroy(nxf_index* idx) {
     if (idx->split) cudaFree(idx->split);
     if (idx->scratch) cudaFree(idx->scratch);
     if (idx->pinned) cudaFreeHost(idx->pinned);
+    if (idx->last_use) cudaEventDestroy(idx->last_use);
+    for (auto& pr : idx->prof_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   }
   delete idx;
 }
@@ -306,6 +344,7 @@ int nxf_reserve(nxf_index* idx, int64_t n_total) {
   NXF_REQUIRE(n_total >= 0 && n_total < (int64_t(1) << 31) - 512, "nxf_reserve: %lld rows exceed the per-device limit", (long long)n_total);
   std::lock_guard<std::mutex> lk(idx->mu);
   DeviceGuard g(idx->device);
+  UseScope use(idx, nullptr);
   return ensure_capacity(idx, n_total, nullptr);
 }
 
@@ -374,6 +413,7 @@ int nxf_add(nxf_index* idx, const void* rows, int64_t n, int src_dtype, int64_t 
   DeviceGuard g(idx->device);
   if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  UseScope use(idx, stream);
   rc = ensure_capacity(idx, idx->n + n, stream);
   if (rc) return rc;
   const size_t esz = dtype_size(idx->store_dtype);
@@ -435,6 +475,7 @@ int nxf_reconstruct(nxf_index* idx, int64_t first, int64_t n, float* dst, int ds
   if (n == 0) return NXF_OK;
   DeviceGuard g(idx->device);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  UseScope use(idx, stream);
   const size_t esz = dtype_size(idx->store_dtype);
   const unsigned char* src = static_cast<const unsigned char*>(idx->data) + static_cast<size_t>(first) * idx->ld * esz;
   if (dst_on_device) {
@@ -679,15 +720,14 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
   return NXF_OK;
 }
 
-extern "C" {
-
-int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, int k, float* out_scores,
-               int64_t* out_ids, int out_on_device, int flags, void* stream_) {
+// out_packed != NULL (device pointer): the rows are written as 8-byte (score, shard-local row) entries instead of the two arrays
+static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, int k, float* out_scores,
+                       int64_t* out_ids, Entry* out_packed, int out_on_device, int flags, void* stream_) {
   NXF_REQUIRE(idx != nullptr, "nxf_search: NULL index");
   NXF_REQUIRE(nq >= 0, "nxf_search: negative query count");
   NXF_REQUIRE(k >= 1 && k <= NXF_MAX_K, "nxf_search: k=%d outside [1, %d]", k, NXF_MAX_K);
   if (nq == 0) return NXF_OK;
-  NXF_REQUIRE(q != nullptr && out_scores != nullptr && out_ids != nullptr, "nxf_search: NULL buffer");
+  NXF_REQUIRE(q != nullptr && ((out_scores != nullptr && out_ids != nullptr) || out_packed != nullptr), "nxf_search: NULL buffer");
   int rc = check_dtype(q_dtype, "nxf_search(q_dtype)");
   if (rc) return rc;
   if (q_ld == 0) q_ld = idx->dim;
@@ -700,6 +740,7 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   DeviceGuard g(idx->device);
   if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  UseScope use(idx, stream);
   const bool l2 = idx->metric == NXF_METRIC_L2;
   const int64_t total = nq * k;
 
@@ -1016,8 +1057,9 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
     mp.arena = arena; mp.qcnt = qcnt; mp.arena_stride = arena_stride; mp.k_fetch = P.k_fetch; mp.k_out = k; mp.metric = idx->metric;
     mp.rescore = P.rescore; mp.q = q_f32; mp.ldq = idx->ld; mp.corpus = idx->data; mp.ld = idx->ld; mp.dim = idx->dim;
     mp.id_offset = idx->id_offset;
-    mp.out_scores = out_on_device ? out_scores + b0 * k : o_scores;
-    mp.out_ids = out_on_device ? out_ids + b0 * k : o_ids;
+    mp.out_scores = out_on_device ? (out_scores ? out_scores + b0 * k : nullptr) : o_scores;
+    mp.out_ids = out_on_device ? (out_ids ? out_ids + b0 * k : nullptr) : o_ids;
+    mp.out_packed = out_packed ? out_packed + b0 * k : nullptr;
     rc = launch_merge_arena(idx->store_dtype, mp, bn, stream);
     if (rc) return rc;
     idx->stats.kernel_launches++;
@@ -1034,6 +1076,20 @@ int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q
   idx->stats.last_chunks = P.chunks;
   idx->stats.last_grid = P.grid;
   return NXF_OK;
+}
+
+extern "C" {
+
+int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, int k, float* out_scores,
+               int64_t* out_ids, int out_on_device, int flags, void* stream_) {
+  if (nq > 0) NXF_REQUIRE(out_scores != nullptr && out_ids != nullptr, "nxf_search: NULL buffer");
+  return search_impl(idx, q, nq, q_dtype, q_ld, q_on_device, k, out_scores, out_ids, nullptr, out_on_device, flags, stream_);
+}
+
+int nxf_search_packed(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int k, nxf_entry* out, int flags, void* stream_) {
+  if (nq > 0) NXF_REQUIRE(out != nullptr, "nxf_search_packed: NULL buffer");
+  static_assert(sizeof(nxf_entry) == sizeof(Entry), "packed entry layout");
+  return search_impl(idx, q, nq, q_dtype, q_ld, 1, k, nullptr, nullptr, reinterpret_cast<Entry*>(out), 1, flags, stream_);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1062,6 +1118,7 @@ int nxf_search_subsets(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
   DeviceGuard g(idx->device);
   if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  UseScope use(idx, stream);
   const size_t qsz = dtype_size(q_dtype);
 
   unsigned char* base = nullptr;
@@ -1149,7 +1206,24 @@ int nxf_merge_topk(const float* scores, const int64_t* ids, int n_lists, int64_t
   DeviceGuard g(device);
   if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
   MergeListsParams p;
-  p.scores = scores; p.ids = ids; p.n_lists = n_lists; p.nq = nq; p.k = k; p.k_out = k_out; p.metric = metric;
+  p.scores = scores; p.ids = ids; p.packed = nullptr; p.n_lists = n_lists; p.nq = nq; p.k = k; p.k_out = k_out; p.metric = metric;
+  p.out_scores = out_scores; p.out_ids = out_ids;
+  return launch_merge_lists(p, static_cast<cudaStream_t>(stream_));
+}
+
+int nxf_merge_packed(const nxf_entry* lists, const int64_t* list_offsets, int n_lists, int64_t nq, int k, int k_out, int metric,
+                     float* out_scores, int64_t* out_ids, int device, void* stream_) {
+  NXF_REQUIRE(lists && list_offsets && out_scores && out_ids, "nxf_merge_packed: NULL buffer");
+  NXF_REQUIRE(n_lists >= 1 && n_lists <= kMaxPackedLists, "nxf_merge_packed: n_lists=%d outside [1, %d]", n_lists, kMaxPackedLists);
+  NXF_REQUIRE(k >= 1 && k_out >= 1 && k_out <= NXF_MAX_K, "nxf_merge_packed: k=%d k_out=%d (max %d)", k, k_out, NXF_MAX_K);
+  NXF_REQUIRE(metric == NXF_METRIC_IP || metric == NXF_METRIC_L2, "nxf_merge_packed: unknown metric %d", metric);
+  NXF_REQUIRE(nq >= 0, "nxf_merge_packed: negative nq");
+  DeviceGuard g(device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  MergeListsParams p;
+  p.scores = nullptr; p.ids = nullptr; p.packed = reinterpret_cast<const Entry*>(lists);
+  for (int l = 0; l < kMaxPackedLists; ++l) p.offs[l] = l < n_lists ? list_offsets[l] : 0;
+  p.n_lists = n_lists; p.nq = nq; p.k = k; p.k_out = k_out; p.metric = metric;
   p.out_scores = out_scores; p.out_ids = out_ids;
   return launch_merge_lists(p, static_cast<cudaStream_t>(stream_));
 }

@@ -20,6 +20,9 @@ namespace nxf {
 void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
+// Raise a kernel's dynamic shared-memory limit once per (kernel, device) instead of one driver round trip per launch (api.cu).
+int ensure_dyn_smem(const void* kernel, int bytes);
+
 #define NXF_CUDA(call)                                                            \
   do {                                                                            \
     cudaError_t _e = (call);                                                      \

@@ -137,8 +137,15 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
       s = (p.metric == NXF_METRIC_L2) ? FLT_MAX : -FLT_MAX;
       id = -1;
     }
-    p.out_scores[qi * p.k_out + j] = s;
-    p.out_ids[qi * p.k_out + j] = id;
+    if (p.out_packed != nullptr) {
+      Entry e;
+      e.score = s;
+      e.row = id < 0 ? -1 : static_cast<int32_t>(id - p.id_offset);  // shard-local: the merge adds the shard's offset
+      p.out_packed[qi * p.k_out + j] = e;
+    } else {
+      p.out_scores[qi * p.k_out + j] = s;
+      p.out_ids[qi * p.k_out + j] = id;
+    }
   }
 }
 
@@ -149,8 +156,10 @@ int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, c
   if (smem > 200 * 1024) { set_error("merge: dim %d too large for the re-score stage", p.dim); return NXF_EUNSUPPORTED; }
 #define NXF_LAUNCH_MERGE(T)                                                                                          \
   do {                                                                                                               \
-    if (smem > 48 * 1024)                                                                                            \
-      NXF_CUDA(cudaFuncSetAttribute(merge_arena_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    if (smem > 48 * 1024) {                                                                                          \
+      const int rc_ = ensure_dyn_smem(reinterpret_cast<const void*>(merge_arena_kernel<T>), (int)smem);              \
+      if (rc_) return rc_;                                                                                           \
+    }                                                                                                                \
     merge_arena_kernel<T><<<static_cast<unsigned>(nq), mg::THREADS, smem, stream>>>(p);                              \
   } while (0)
   switch (store_dtype) {
@@ -292,7 +301,7 @@ int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, in
   if (nq <= 0) return NXF_OK;
   if (grid > 256) { set_error("seed: %d lists per query (max 256)", grid); return NXF_EUNSUPPORTED; }
   const size_t smem = static_cast<size_t>(std::min<int64_t>(SEED_MAX_KEYS, static_cast<int64_t>(grid) * cap)) * sizeof(uint32_t);
-  NXF_CUDA(cudaFuncSetAttribute(seed_tau_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEED_MAX_KEYS * 4));
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(seed_tau_lists_kernel), SEED_MAX_KEYS * 4)) return rc;
   seed_tau_lists_kernel<<<static_cast<unsigned>(nq), mg::THREADS, smem, stream>>>(cand, cnt_g, grid, nq_pad, cap, k_fetch, tau_g);
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
@@ -349,7 +358,8 @@ int launch_verify_counts(uint32_t* qcnt, uint32_t* tau_g, int64_t nq, int need, 
 }
 
 // ---- multi-list merge (multi-GPU shard merge) ---------------------------------------------------
-__global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(MergeListsParams p) {
+template <bool PACKED>
+__global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(const __grid_constant__ MergeListsParams p) {
   __shared__ uint64_t keys[mg::MAXK];
   __shared__ int64_t pay[mg::MAXK];
   __shared__ uint32_t hist[256];
@@ -362,10 +372,15 @@ __global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(MergeListsPara
   const bool l2 = p.metric == NXF_METRIC_L2;
   auto score_at = [&](int i) -> float {
     const int l = i / p.k, j = i - l * p.k;
+    if (PACKED) return p.packed[(static_cast<int64_t>(l) * p.nq + qi) * p.k + j].score;
     return p.scores[(static_cast<int64_t>(l) * p.nq + qi) * p.k + j];
   };
   auto id_at = [&](int i) -> int64_t {
     const int l = i / p.k, j = i - l * p.k;
+    if (PACKED) {
+      const int32_t row = p.packed[(static_cast<int64_t>(l) * p.nq + qi) * p.k + j].row;
+      return row < 0 ? -1 : static_cast<int64_t>(row) + p.offs[l];
+    }
     return p.ids[(static_cast<int64_t>(l) * p.nq + qi) * p.k + j];
   };
   // key 0 for padding (id < 0) so that it sorts last in either metric
@@ -434,7 +449,8 @@ __global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(MergeListsPara
 
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream) {
   if (p.nq <= 0) return NXF_OK;
-  merge_lists_kernel<<<static_cast<unsigned>(p.nq), mg::THREADS, 0, stream>>>(p);
+  if (p.packed != nullptr) merge_lists_kernel<true><<<static_cast<unsigned>(p.nq), mg::THREADS, 0, stream>>>(p);
+  else merge_lists_kernel<false><<<static_cast<unsigned>(p.nq), mg::THREADS, 0, stream>>>(p);
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
 }

@@ -135,6 +135,7 @@ struct MergeArenaParams {
   int64_t id_offset;
   float* out_scores;  // [nq, k_out]
   int64_t* out_ids;   // [nq, k_out]
+  Entry* out_packed;  // not NULL: write [nq, k_out] (score, shard-local row; -1 = padding) entries instead (nxf_search_packed)
 };
 
 struct SubsetParams {
@@ -155,9 +156,12 @@ struct SubsetParams {
   uint32_t* err;           // bit 0: a row id outside [0, n_rows); bit 1: malformed offsets
 };
 
+constexpr int kMaxPackedLists = 64;
 struct MergeListsParams {
   const float* scores;  // [n_lists, nq, k]
   const int64_t* ids;   // [n_lists, nq, k]
+  const Entry* packed;  // not NULL: [n_lists, nq, k] (score, list-local row) entries instead of scores / ids; global id = row + offs[list]
+  int64_t offs[kMaxPackedLists];
   int n_lists;
   int64_t nq;
   int k;

@@ -345,7 +345,7 @@ static int launch_pool_mean_split(const void* hidden, const int64_t* mask, int64
   const size_t smem = static_cast<size_t>(G) * H * 4;
   const size_t part_bytes = static_cast<size_t>(B) * splits * H * 4;
   auto kern = pool_mean_split_kernel<T, O, VEC>;
-  if (smem > 48 * 1024) NXF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  if (smem > 48 * 1024) { if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), static_cast<int>(smem))) return rc; }
   const char* ws_env = getenv("NXF_POOL_WS_CACHE");  // read per call
   const bool cached_ws = ws_env ? atoi(ws_env) != 0 : NXF_POOL_WS_CACHE_DEFAULT != 0;
   if (cached_ws) {
@@ -393,7 +393,7 @@ static int launch_pool_t(const void* hidden, const int64_t* mask, int64_t B, int
   const size_t smem = static_cast<size_t>(groups) * H * 4;
   if (smem > 200 * 1024) { set_error("pool_normalize: hidden size %lld too large", (long long)H); return NXF_EUNSUPPORTED; }
   auto kern = pool_norm_kernel<T, O, VEC>;
-  if (smem > 48 * 1024) NXF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  if (smem > 48 * 1024) { if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), static_cast<int>(smem))) return rc; }
   kern<<<static_cast<unsigned>(B), k0::THREADS, smem, stream>>>((const T*)hidden, mask, B, L, H, pooling, normalize, eps, (O*)out, groups);
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;

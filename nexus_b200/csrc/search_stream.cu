@@ -251,7 +251,7 @@ size_t k2_smem_bytes(int64_t ld, int elem_size, int nq_t, int rw, int stages) {
 
 template <typename T, int NQ, int RW>
 static int launch_k2_t(const K2Params& p, int grid, size_t smem, cudaStream_t stream) {
-  NXF_CUDA(cudaFuncSetAttribute(k2_stream_kernel<T, NQ, RW>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(k2_stream_kernel<T, NQ, RW>), static_cast<int>(smem))) return rc;
   k2_stream_kernel<T, NQ, RW><<<grid, k2::THREADS, smem, stream>>>(p);
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;

@@ -383,7 +383,8 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* co
   const bool l2 = p.half_norm != nullptr;
 #define NXF_K2T_LAUNCH3(B, L, S)                                                                                                      \
   do {                                                                                                                                \
-    NXF_CUDA(cudaFuncSetAttribute(k2t_stream_kernel<B, L, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));  \
+    rc = ensure_dyn_smem(reinterpret_cast<const void*>(k2t_stream_kernel<B, L, S>), static_cast<int>(smem));                          \
+    if (rc) return rc;                                                                                                                \
     k2t_stream_kernel<B, L, S><<<grid, k2t::threads(S), smem, stream>>>(tq, tc, p);                                                   \
   } while (0)
 #define NXF_K2T_LAUNCH(B, L)                     \

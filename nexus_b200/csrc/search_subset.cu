@@ -167,8 +167,10 @@ int launch_subset_search(int store_dtype, const SubsetParams& p, int64_t nq, cud
   if (smem > 200 * 1024) { set_error("search_subsets: dim %d too large", p.dim); return NXF_EUNSUPPORTED; }
 #define NXF_LAUNCH_SUBSET3(T, LPR, L2)                                                                                          \
   do {                                                                                                                          \
-    if (smem > 48 * 1024)                                                                                                       \
-      NXF_CUDA(cudaFuncSetAttribute(subset_search_kernel<T, LPR, L2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    if (smem > 48 * 1024) {                                                                                                     \
+      const int rc_ = ensure_dyn_smem(reinterpret_cast<const void*>(subset_search_kernel<T, LPR, L2>), (int)smem);              \
+      if (rc_) return rc_;                                                                                                      \
+    }                                                                                                                           \
     subset_search_kernel<T, LPR, L2><<<static_cast<unsigned>(nq), mg::THREADS, smem, stream>>>(p);                              \
   } while (0)
 #define NXF_LAUNCH_SUBSET2(T, LPR)                                      \

@@ -28,6 +28,8 @@
 // (their thresholds, counters and candidate buffers never move) while all clusters consume the same round of the
 // corpus at different offsets: each corpus tile comes from HBM once and from L2 for the other query tiles.  A soft
 // (timeout-guarded) round barrier between the producers keeps the clusters within one round of each other.
+#include <mutex>
+
 #include "params.cuh"
 
 namespace nxf {
@@ -473,7 +475,29 @@ static PFN_encodeTiled get_encode_fn() {
 }
 
 // rows x ld 16-bit matrix, box = 64 elements (128 B, one swizzle atom) x box_rows
+// The same few maps are asked for again and again (five K1 launches per search over one corpus and one query buffer; the serve
+// path repeats the identical search shape per request): a small cache keyed by everything the encoding depends on.
+namespace {
+struct TmapSlot { const void* base; int64_t rows, ld; int box_rows; bool bf16, valid; CUtensorMap map; };
+std::mutex g_tmap_mu;
+TmapSlot g_tmap_cache[16];
+unsigned g_tmap_next = 0;
+}  // namespace
+
+static int encode_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, int64_t ld, int box_rows, bool bf16);
+
 int make_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, int64_t ld, int box_rows, bool bf16) {
+  std::lock_guard<std::mutex> lk(g_tmap_mu);
+  for (const TmapSlot& s : g_tmap_cache)
+    if (s.valid && s.base == base && s.rows == rows && s.ld == ld && s.box_rows == box_rows && s.bf16 == bf16) { *m = s.map; return NXF_OK; }
+  const int rc = encode_tmap_2d_sw128(m, base, rows, ld, box_rows, bf16);
+  if (rc) return rc;
+  TmapSlot& s = g_tmap_cache[g_tmap_next++ % 16];
+  s.base = base; s.rows = rows; s.ld = ld; s.box_rows = box_rows; s.bf16 = bf16; s.map = *m; s.valid = true;
+  return NXF_OK;
+}
+
+static int encode_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, int64_t ld, int box_rows, bool bf16) {
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return NXF_ECUDA; }
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(ld), static_cast<cuuint64_t>(rows)};
@@ -491,7 +515,7 @@ template <int CG, bool BF16, int SETS>
 static int launch_k1_t(const CUtensorMap& tq, const CUtensorMap& tc, const K1Params& p, int grid, cudaStream_t stream) {
   using C = k1::Cfg<CG>;
   auto kern = k1_search_kernel<CG, BF16, SETS>;
-  NXF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), C::SMEM_BYTES)) return rc;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(static_cast<unsigned>(grid));
   cfg.blockDim = dim3(128 + 128 * SETS);

@@ -34,9 +34,72 @@ def _store_dtype_default() -> str:
     return os.environ.get("NEXUS_B200_STORE_DTYPE", "f32")
 
 
+class _ItemCache:
+    """Row N3: ``BaseRetriever.eval_step`` builds ``IndexFlatIP(d)`` -> ``index_cpu_to_gpu`` -> ``add(item_vectors)``
+    again for EVERY evaluation batch (modeling.py:182-195, called per batch from evaluation/recommendation/evaluator.py:115-134)
+    with the same item matrix.  The shim keeps the device shard it built and hands it to the next identical ``add``:
+
+    * same tensor OBJECT (a weak reference is still alive, so its storage cannot have been recycled), same ``data_ptr`` and same
+      ``_version`` -> same contents, no device work at all (Inner-product / Euclidean scorers pass ``self.item_vectors`` itself);
+    * otherwise (the Cosine scorer normalises into a NEW tensor each batch, modeling.py:188) a checksum of the rows decides: two
+      device reductions over the tensor's bits and one 16-byte read-back instead of a convert + copy of all N rows.
+
+    A few entries per process (``NEXUS_B200_SHIM_CACHE`` = entries, 0 disables).  A cached shard is shared read-only: a further
+    ``add`` / ``reset`` on an object that holds one first takes a private copy."""
+
+    def __init__(self):
+        self.entries = []       # dicts: key, ref, ptr, version, checksum, impl
+
+    @staticmethod
+    def capacity() -> int:
+        try:
+            return max(0, int(os.environ.get("NEXUS_B200_SHIM_CACHE", "2")))
+        except ValueError:
+            return 2
+
+    @staticmethod
+    def checksum(x):
+        import torch
+        v = x.contiguous().view(-1).view(torch.int32 if x.element_size() == 4 else torch.int16)
+        both = torch.stack([v.sum(dtype=torch.int64), v[::3].sum(dtype=torch.int64)])
+        return tuple(both.tolist())
+
+    def lookup(self, x, key):
+        for e in self.entries:
+            if e["key"] != key:
+                continue
+            if e["ref"]() is x and e["ptr"] == x.data_ptr() and e["version"] == x._version:
+                return e["impl"], "identity"
+        cs = None
+        for e in self.entries:
+            if e["key"] != key:
+                continue
+            cs = cs or self.checksum(x)
+            if e["checksum"] == cs:
+                return e["impl"], "checksum"
+        return None, cs
+
+    def store(self, x, key, impl, cs=None):
+        import weakref
+        cap = self.capacity()
+        if cap == 0:
+            return
+        self.entries.insert(0, {"key": key, "ref": weakref.ref(x), "ptr": x.data_ptr(), "version": x._version,
+                                "checksum": cs or self.checksum(x), "impl": impl})
+        del self.entries[cap:]
+
+    def clear(self):
+        self.entries.clear()
+
+
+_item_cache = _ItemCache()
+cache_stats = {"identity": 0, "checksum": 0, "miss": 0}
+
+
 class _LazyFlat:
     """IndexFlat{IP,L2}(d): materialises a device index on first use (device chosen by
     index_cpu_to_gpu / index_cpu_to_all_gpus, else the current device)."""
+    __nexus_b200_lazy__ = True
 
     def __init__(self, d: int, metric: int, store_dtype: Optional[str] = None):
         self.d = int(d)
@@ -46,6 +109,7 @@ class _LazyFlat:
         self._store_dtype = store_dtype or _store_dtype_default()
         self._impl = None
         self._devices = None      # None -> current device; list -> sharded
+        self._shared = False      # _impl is also held by the item cache: copy before mutating
 
     def _ensure(self, like=None):
         if self._impl is None:
@@ -64,14 +128,44 @@ class _LazyFlat:
     def train(self, x=None):
         return None
 
+    def _own(self):
+        """Take a private copy of a shard that the item cache also holds (device-to-device, fp32 round trip of the stored values)."""
+        if self._shared and self._impl is not None:
+            import torch
+            old = self._impl
+            rows = torch.empty((old.ntotal, old.d), dtype=torch.float32, device=f"cuda:{old.device}")
+            old.reconstruct_into(rows)
+            self._impl = FlatIndex(self.d, old.metric, old.store_dtype, device=old.device)
+            if old.ntotal:
+                self._impl.add(rows)
+        self._shared = False
+
     def add(self, x):
+        single = self._devices is None or len(self._devices) == 1
+        if self._impl is None and single and _is_tensor(x) and x.is_cuda and x.dim() == 2 and _ItemCache.capacity() > 0:
+            dev = self._devices[0] if self._devices else x.device.index
+            if dev == x.device.index:
+                key = (dev, self.d, int(self.metric_type), self._store_dtype, tuple(x.shape), str(x.dtype))
+                impl, how = _item_cache.lookup(x, key)
+                if impl is not None:
+                    cache_stats[how] += 1
+                    self._impl, self._shared = impl, True
+                    return
+                cache_stats["miss"] += 1
+                self._ensure(x).add(x)
+                _item_cache.store(x, key, self._impl, how)
+                self._shared = True
+                return
+        self._own()
         self._ensure(x).add(x)
 
     def search(self, x, k):
         return self._ensure(x).search(x, k)
 
     def reset(self):
-        if self._impl is not None:
+        if self._shared:
+            self._impl, self._shared = None, False
+        elif self._impl is not None:
             self._impl.reset()
 
     def reconstruct_n(self, first=0, n=None):
@@ -133,16 +227,33 @@ def get_num_gpus() -> int:
 
 
 def index_cpu_to_gpu(res, device: int, index, options=None):
-    if index.ntotal:
-        rows = index.reconstruct_n()
-        new = _LazyFlat(index.d, index.metric_type, index._store_dtype)
-        new._devices = [int(device)]
-        new.add(rows)
-        return new
-    index._devices = [int(device)]
-    if options is not None and getattr(options, "useFloat16", False):
-        index._store_dtype = "f16"
-    return index
+    """``faiss.index_cpu_to_gpu(res, device, index)`` (modeling.py:194 passes ``index=`` by keyword; recommendation/base.py:115-116
+    moves a populated index read from disk).  An empty index only records its device.  A populated one that already lives on
+    ``device`` with the requested storage type is returned as it is (no second upload); otherwise its rows move device to device
+    (or host to device for a sharded source) into a new shard.  ``options.useFloat16`` selects fp16 storage in both cases."""
+    device = int(device)
+    want16 = options is not None and getattr(options, "useFloat16", False)
+    store = "f16" if want16 else index._store_dtype
+    impl = index._impl
+    if impl is None or index.ntotal == 0:
+        if impl is not None and not (isinstance(impl, FlatIndex) and impl.device == device and impl.store_dtype == store):
+            index._impl, index._shared = None, False     # an emptied shard on another device / of another type: rebuilt on first use
+        index._devices = [device]
+        index._store_dtype = store
+        return index
+    if isinstance(impl, FlatIndex) and impl.device == device and impl.store_dtype == store:
+        index._devices = [device]
+        return index
+    new = _LazyFlat(index.d, index.metric_type, store)
+    new._devices = [device]
+    if isinstance(impl, FlatIndex):
+        import torch
+        rows = torch.empty((impl.ntotal, impl.d), dtype=torch.float32, device=f"cuda:{impl.device}")
+        impl.reconstruct_into(rows)
+        new._ensure().add(rows.to(f"cuda:{device}"))
+    else:
+        new._ensure().add(index.reconstruct_n())
+    return new
 
 
 def index_cpu_to_all_gpus(index, co=None, ngpu: int = -1):

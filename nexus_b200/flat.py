@@ -81,6 +81,10 @@ def _as_rows(x, want_dim: Optional[int], what: str) -> _Buf:
             x = x.float()
         if x.stride(1) != 1 or (x.shape[0] > 1 and x.stride(0) < x.shape[1]):
             x = x.contiguous()
+        elif not x.is_cuda and x.shape[0] > 1 and x.stride(0) != x.shape[1]:
+            # a strided HOST view (big[:, off:off+d]): the host paths copy n*ld contiguous elements from data_ptr, which would
+            # run past the end of the storage on the last row -- densify (device views are read element-wise and may stay)
+            x = x.contiguous()
         b.ptr, b.dtype, b.ld = x.data_ptr(), codes[x.dtype], (x.stride(0) if x.shape[0] > 1 else x.shape[1])
         b.on_device = 1 if x.is_cuda else 0
         b.device = x.device.index if x.is_cuda else None
@@ -131,6 +135,7 @@ class FlatIndex:
         self.nprobe = 1          # settable and ignored: an exact scan probes everything
         self.is_trained = True
         self.search_flags = L.SEARCH_DEFAULT
+        self._id_offset = 0
 
     # ---- Faiss-shaped attributes ----
     @property
@@ -178,6 +183,11 @@ class FlatIndex:
 
     def set_id_offset(self, offset: int) -> None:
         L.check(self._lib.nxf_set_id_offset(self._h, int(offset)))
+        self._id_offset = int(offset)
+
+    @property
+    def id_offset(self) -> int:
+        return self._id_offset
 
     def add(self, x) -> None:
         """Append rows (utils.py:189, modeling.py:195).  The index keeps its own converted copy."""
@@ -194,6 +204,14 @@ class FlatIndex:
         out = np.empty((n, self.d), dtype=np.float32)
         L.check(self._lib.nxf_reconstruct(self._h, int(first), int(n), out.ctypes.data, 0, _stream_ptr(self._device)))
         return out
+
+    def reconstruct_into(self, out, first: int = 0) -> None:
+        """Rows ``[first, first + out.shape[0])`` as fp32 into a CUDA tensor on the index's device (no host round trip)."""
+        torch = _torch()
+        if not (out.is_cuda and out.device.index == self._device and out.dtype == torch.float32 and out.is_contiguous()
+                and out.dim() == 2 and out.shape[1] == self.d):
+            raise ValueError(f"reconstruct_into: need a contiguous float32 CUDA tensor [n, {self.d}] on cuda:{self._device}")
+        L.check(self._lib.nxf_reconstruct(self._h, int(first), int(out.shape[0]), out.data_ptr(), 1, _stream_ptr(self._device)))
 
     def reconstruct(self, i: int) -> np.ndarray:
         return self.reconstruct_n(i, 1)[0]
@@ -227,6 +245,24 @@ class FlatIndex:
         I = np.empty((b.n, k), dtype=np.int64)
         L.check(self._lib.nxf_search(self._h, b.ptr, b.n, b.dtype, b.ld, 0, k, D.ctypes.data, I.ctypes.data, 0, flags, stream))
         return D, I
+
+    def search_packed(self, x, k: int, flags: Optional[int] = None, out=None):
+        """The shard's contribution to a row-sharded search: ``x`` a CUDA tensor on this device -> int64 CUDA tensor ``[n, k]``
+        whose 8-byte elements are ``(float32 score, int32 shard-local row)`` pairs (``nxf_entry``; row -1 = padding), rows
+        best-first.  One buffer, so the per-shard lists travel in ONE collective; :func:`merge_packed` turns the gathered lists
+        into ``(D, I)`` with global ids.  Asynchronous on the current stream."""
+        torch = _torch()
+        b = _as_rows(x, self.d, "search_packed")
+        if b.kind != "torch" or not b.on_device or b.device != self._device:
+            raise ValueError(f"search_packed: queries must be a CUDA tensor on cuda:{self._device}")
+        k = int(k)
+        flags = self.search_flags if flags is None else flags
+        if out is None:
+            out = torch.empty((b.n, k), dtype=torch.int64, device=b.keep.device)
+        elif tuple(out.shape) != (b.n, k) or out.dtype != torch.int64 or not out.is_contiguous() or out.device != b.keep.device:
+            raise ValueError("search_packed: out must be a contiguous int64 CUDA tensor [n, k] on the index's device")
+        L.check(self._lib.nxf_search_packed(self._h, b.ptr, b.n, b.dtype, b.ld, k, out.data_ptr(), flags, _stream_ptr(self._device)))
+        return out
 
     def search_subsets(self, x, offsets, rows, k: int) -> Tuple:
         """Per-query candidate lists: query ``i`` ranks the index rows ``rows[offsets[i]:offsets[i+1]]`` (CSR) and gets the
@@ -299,6 +335,37 @@ def merge_topk(scores, ids, k_out: Optional[int] = None, metric: str = "ip"):
     dev = scores.device.index
     L.check(L.load().nxf_merge_topk(scores.data_ptr(), ids.data_ptr(), n_lists, nq, k, k_out, _METRICS[metric],
                                     D.data_ptr(), I.data_ptr(), dev, _stream_ptr(dev)))
+    return D, I
+
+
+def packed_padding(metric: str = "ip") -> int:
+    """The int64 value of a padding ``nxf_entry`` (row -1, score -FLT_MAX for inner product / +FLT_MAX for L2)."""
+    fill = np.finfo(np.float32).max if metric == "l2" else -np.finfo(np.float32).max
+    return int(np.array([(fill, -1)], dtype=[("score", "<f4"), ("row", "<i4")]).view(np.int64)[0])
+
+
+def merge_packed(lists, offsets, k_out: Optional[int] = None, metric: str = "ip", out=None):
+    """Merge gathered per-shard packed lists on the device: ``lists`` int64 CUDA tensor ``[n_lists, nq, k]`` of ``nxf_entry``
+    pairs (see :meth:`FlatIndex.search_packed`), ``offsets`` the first global row of every shard ->
+    ``(D float32 [nq, k_out], I int64 [nq, k_out])`` with global ids.  K3 reading 8-byte entries: the device-side replacement of
+    Faiss IndexShards' host merge (utils.py:178-183)."""
+    torch = _torch()
+    if not lists.is_cuda or lists.dtype != torch.int64 or lists.dim() != 3:
+        raise ValueError("merge_packed: lists must be an int64 CUDA tensor [n_lists, nq, k] (there is no CPU path)")
+    lists = lists.contiguous()
+    n_lists, nq, k = lists.shape
+    if len(offsets) != n_lists:
+        raise ValueError(f"merge_packed: {len(offsets)} offsets for {n_lists} lists")
+    k_out = k if k_out is None else int(k_out)
+    if out is None:
+        D = torch.empty((nq, k_out), dtype=torch.float32, device=lists.device)
+        I = torch.empty((nq, k_out), dtype=torch.int64, device=lists.device)
+    else:
+        D, I = out
+    offs = (C.c_int64 * n_lists)(*[int(o) for o in offsets])
+    dev = lists.device.index
+    L.check(L.load().nxf_merge_packed(lists.data_ptr(), offs, n_lists, nq, k, k_out, _METRICS[metric], D.data_ptr(), I.data_ptr(),
+                                      dev, _stream_ptr(dev)))
     return D, I
 
 

@@ -77,8 +77,13 @@ def search(faiss_index: Any, k: int = 100, query_embeddings: Optional[np.ndarray
     """Search the index (utils.py:194-230): returns ``(all_scores float32 [Q,k], all_indices int64 [Q,k])``."""
     if query_embeddings is None:
         query_embeddings = np.load(load_path)               # utils.py:212-213
-    if isinstance(faiss_index, (FlatIndex, ShardedFlatIndex)):
-        scores, ids = faiss_index.search(query_embeddings, k)
+    # every engine-backed object takes the WHOLE query matrix in one call: FlatIndex / ShardedFlatIndex, the shim's lazily
+    # materialised Faiss-shaped objects (index_factory, read_index, index_cpu_to_all_gpus) and a DistributedFlatIndex
+    engine = faiss_index
+    if getattr(faiss_index, "__nexus_b200_lazy__", False):
+        engine = faiss_index._ensure(query_embeddings)
+    if isinstance(engine, (FlatIndex, ShardedFlatIndex)) or getattr(engine, "__nexus_b200_engine__", False):
+        scores, ids = engine.search(query_embeddings, k)
         if not isinstance(scores, np.ndarray):              # torch in -> torch out; this function returns numpy
             scores, ids = scores.cpu().numpy(), ids.cpu().numpy()
         return scores, ids

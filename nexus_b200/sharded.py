@@ -5,12 +5,14 @@ Nexus/evaluation/text_retrieval/utils.py:178-183): every GPU holds N/G rows, eve
 shard, per-shard top-k lists are merged on the host.  Here the merge stays on the device:
 
   * :class:`ShardedFlatIndex`      one process driving G devices (what ``index()`` builds when several GPUs
-                                   are visible, like the reference): per-shard lists are copied peer-to-peer
-                                   over NVLink to the first device and merged by ``nxf_merge_topk``.
+                                   are visible, like the reference): every shard writes its ``[Q,k]`` list as
+                                   8-byte ``(score, shard-local row)`` entries (``nxf_search_packed``), the lists
+                                   are copied peer-to-peer over NVLink to the home device (stream-ordered by
+                                   events, no host synchronisation) and merged by ``nxf_merge_packed``.
   * :class:`DistributedFlatIndex`  one process per GPU (torchrun): the corpus rows never move after ``add``;
-                                   per-shard ``(score, global id)`` lists are exchanged with ONE NCCL
-                                   all-gather ([Q,k] float32 + [Q,k] int64 per rank) and merged by the same
-                                   kernel on every rank.
+                                   the packed per-shard lists are exchanged with ONE NCCL all-gather of
+                                   Q*k*8 bytes per rank into a preallocated buffer and merged by the same kernel
+                                   on every rank, which adds each shard's row offset.
 """
 from __future__ import annotations
 
@@ -18,7 +20,7 @@ from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from .flat import FlatIndex, _is_tensor, merge_topk
+from .flat import FlatIndex, _is_tensor, merge_packed, merge_topk, packed_padding
 
 
 def shard_bounds(n: int, world: int) -> List[Tuple[int, int]]:
@@ -90,33 +92,49 @@ class ShardedFlatIndex:
             last.add(part)
 
     def search(self, x, k: int):
+        """Every shard searches on its own device (asynchronous, packed output); the lists reach the home device over NVLink
+        behind events -- the host never waits for a shard -- and one merge kernel produces ``(D, I)`` with global ids."""
         import torch
         k = int(k)
         was_numpy = not _is_tensor(x)
-        xt = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float32) if np.asarray(x).dtype not in (np.float16, np.float32) else np.asarray(x))) if was_numpy else x
+        if was_numpy:
+            a = np.asarray(x)
+            xt = torch.from_numpy(np.ascontiguousarray(a if a.dtype in (np.float16, np.float32) else a.astype(np.float32)))
+        else:
+            xt = x
+        if xt.dim() == 1:
+            xt = xt.unsqueeze(0)
         was_cuda = (not was_numpy) and xt.is_cuda
         home = self.devices[0] if not was_cuda else xt.device.index
-        parts_d, parts_i = [], []
-        # launch every shard's search (asynchronous on its own device), then gather over NVLink
-        for shard in self.shards:
-            if shard.ntotal == 0:
-                continue
-            q = xt.to(f"cuda:{shard.device}", non_blocking=True)
-            with torch.cuda.device(shard.device):
-                D, I = shard.search(q, k)
-            parts_d.append(D)
-            parts_i.append(I)
-        if not parts_d:
-            nq = xt.shape[0]
-            D = torch.full((nq, k), -torch.finfo(torch.float32).max if self._metric != "l2" else torch.finfo(torch.float32).max)
+        nq = int(xt.shape[0])
+        metric = "l2" if self._metric == "l2" else "ip"
+        active = [s_ for s_ in self.shards if s_.ntotal > 0]
+        if not active:
+            fill = torch.finfo(torch.float32).max * (1 if metric == "l2" else -1)
+            D = torch.full((nq, k), fill)
             I = torch.full((nq, k), -1, dtype=torch.int64)
             return (D.numpy(), I.numpy()) if was_numpy else (D.to(xt.device), I.to(xt.device))
-        for shard_d in parts_d:
-            torch.cuda.current_stream(shard_d.device).synchronize()
+        src_stream = torch.cuda.current_stream(xt.device) if was_cuda else None
+        parts, events = [], []
+        for shard in active:
+            with torch.cuda.device(shard.device):
+                st = torch.cuda.current_stream(shard.device)
+                if src_stream is not None and shard.device != xt.device.index:
+                    st.wait_stream(src_stream)                  # the queries were produced on the home device's stream
+                q = xt.to(f"cuda:{shard.device}", non_blocking=True)
+                P = shard.search_packed(q, k)
+                ev = torch.cuda.Event()
+                ev.record(st)
+            parts.append(P)
+            events.append(ev)
         with torch.cuda.device(home):
-            Ds = torch.stack([t.to(f"cuda:{home}") for t in parts_d])
-            Is = torch.stack([t.to(f"cuda:{home}") for t in parts_i])
-            D, I = merge_topk(Ds, Is, k, "l2" if self._metric == "l2" else "ip")
+            hs = torch.cuda.current_stream(home)
+            lists = torch.empty((len(active), nq, k), dtype=torch.int64, device=f"cuda:{home}")
+            for g, (P, ev) in enumerate(zip(parts, events)):
+                hs.wait_event(ev)
+                lists[g].copy_(P, non_blocking=True)            # NVLink peer copy (a local copy for the home shard)
+                P.record_stream(hs)
+            D, I = merge_packed(lists, [s_.id_offset for s_ in active], k, metric)
         if was_numpy:
             return D.cpu().numpy(), I.cpu().numpy()
         if not was_cuda:
@@ -126,6 +144,7 @@ class ShardedFlatIndex:
 
 class DistributedFlatIndex:
     """One process per GPU over ``torch.distributed`` (NCCL).  Rank r holds shard r."""
+    __nexus_b200_engine__ = True
 
     def __init__(self, d: int, metric: str = "ip", store_dtype: str = "bf16", device=None, group=None):
         import torch
@@ -140,6 +159,8 @@ class DistributedFlatIndex:
         self.local = FlatIndex(d, metric, store_dtype, device=device)
         self._metric = metric
         self._ntotal_global = 0
+        self._offsets = [0] * self.world       # first global row of every rank's shard
+        self._bufs = {}                        # (Q, k) -> preallocated exchange buffers
 
     @property
     def ntotal(self) -> int:
@@ -160,32 +181,64 @@ class DistributedFlatIndex:
         if hi > lo:
             self.local.add(x[lo:hi])
         self._ntotal_global = n
+        self._offsets = [b[0] for b in shard_bounds(n, self.world)]
 
     def add_local(self, x_local, global_offset: int, n_global: int) -> None:
         """Rank-local rows that already are this rank's shard (e.g. straight from a data-parallel encoder:
         the embeddings are never all-gathered, unlike mmeb_v2/eval_embedding.py:127-131)."""
+        import torch.distributed as dist
         self.local.set_id_offset(int(global_offset))
         self.local.add(x_local)
         self._ntotal_global = int(n_global)
+        offs = [None] * self.world
+        dist.all_gather_object(offs, int(global_offset), group=self.group)     # once per build: every rank's first global row
+        self._offsets = [int(o) for o in offs]
 
     def reset(self) -> None:
         self.local.reset()
         self._ntotal_global = 0
 
+    def _buffers(self, Q: int, k: int, device):
+        import torch
+        key = (Q, k)
+        b = self._bufs.get(key)
+        if b is None:
+            if len(self._bufs) > 8:
+                self._bufs.clear()
+            b = (torch.empty((Q, k), dtype=torch.int64, device=device), torch.empty((self.world, Q, k), dtype=torch.int64, device=device))
+            self._bufs[key] = b
+        return b
+
     def search(self, q, k: int, gather=None, merge=None, exchange: str = "auto"):
         """``q``: the same [Q, D] CUDA tensor on every rank.  Returns the merged ``(D, I)`` on every rank.
-        ``exchange``: ``"gather"`` = one all-gather of the per-shard ``[Q, k]`` lists + merge on every rank (the north star's form);
-        ``"partition"`` = rank r receives only the lists of its own block of queries (all-to-all), merges them and the final blocks
-        are all-gathered -- 2/world of the bytes, for large ``Q*k``; ``"auto"`` picks by size.
-        ``gather`` / ``merge`` are injection points for the CPU (gloo) tests of the exchange logic."""
-        D, I = self.local.search(q, int(k))
+        ``exchange``: ``"gather"`` = ONE all-gather of the per-shard ``[Q, k]`` lists as 8-byte ``(score, shard-local row)``
+        entries into a preallocated buffer + the merge kernel on every rank, which adds the shards' row offsets (the north
+        star's form); ``"partition"`` = rank r receives only the lists of its own block of queries (all-to-all), merges them and
+        the final blocks are all-gathered -- 2/world of the bytes, for large ``Q*k``; ``"auto"`` picks by size.
+        ``gather`` / ``merge`` are injection points for the CPU (gloo) tests of the exchange logic (unpacked lists)."""
+        import torch
+        import torch.distributed as dist
+        k = int(k)
         metric = "l2" if self._metric == "l2" else "ip"
+        if gather is None and merge is None and not (_is_tensor(q) and q.is_cuda):
+            a = q if _is_tensor(q) else torch.from_numpy(np.ascontiguousarray(np.asarray(q)))
+            q = (a if a.dtype in (torch.float16, torch.bfloat16, torch.float32) else a.float()).to(f"cuda:{self.local.device}")
+        if gather is not None or merge is not None:
+            D, I = self.local.search(q, k)
+            if exchange == "partition":
+                return exchange_partitioned(D, I, self.world, k, metric, self.group, merge or merge_topk)
+            Ds, Is = (gather or all_gather_lists)(D, I, self.world, self.group)
+            return (merge or merge_topk)(Ds, Is, k, metric)
+        Q = int(q.shape[0])
         if exchange == "auto":
-            exchange = "partition" if (self.world > 2 and D.numel() * 12 * self.world >= PARTITION_MIN_BYTES and gather is None) else "gather"
+            exchange = "partition" if (self.world > 2 and Q * k * 8 * self.world >= PARTITION_MIN_BYTES) else "gather"
         if exchange == "partition":
-            return exchange_partitioned(D, I, self.world, int(k), metric, self.group, merge or merge_topk)
-        Ds, Is = (gather or all_gather_lists)(D, I, self.world, self.group)
-        return (merge or merge_topk)(Ds, Is, int(k), metric)
+            P = self.local.search_packed(q, k)
+            return exchange_partitioned_packed(P, self._offsets, self.world, k, metric, self.group)
+        mine, lists = self._buffers(Q, k, q.device)
+        self.local.search_packed(q, k, out=mine)
+        dist.all_gather_into_tensor(lists, mine, group=self.group)          # the one exchange step: Q*k*8 bytes per rank
+        return merge_packed(lists, self._offsets, k, metric)
 
 
 # all-gather volume (bytes received per rank) from which the query-partitioned exchange is used: below, one collective wins
@@ -221,6 +274,26 @@ def exchange_partitioned(D, I, world: int, k: int, metric: str = "ip", group=Non
     else:
         dist.all_gather(list(Do.view(world, Qb, k).unbind(0)), Dm, group=group)
         dist.all_gather(list(Io.view(world, Qb, k).unbind(0)), Im, group=group)
+    return Do[:Q], Io[:Q]
+
+
+def exchange_partitioned_packed(P, offsets, world: int, k: int, metric: str = "ip", group=None):
+    """:func:`exchange_partitioned` on packed lists (int64 ``[Q, k]`` of ``nxf_entry``): one all-to-all of 8-byte entries, the merge
+    kernel adds the shard offsets, then the merged ``(D, I)`` blocks are all-gathered."""
+    import torch
+    import torch.distributed as dist
+    Q = int(P.shape[0])
+    Qb = (Q + world - 1) // world
+    if Qb * world != Q:
+        P = torch.cat([P, torch.full((Qb * world - Q, k), packed_padding(metric), dtype=P.dtype, device=P.device)], 0)
+    P = P.contiguous()
+    Pr = torch.empty_like(P)
+    dist.all_to_all_single(Pr, P, group=group)           # Pr[g*Qb:(g+1)*Qb] = shard g's lists for my query block
+    Dm, Im = merge_packed(Pr.view(world, Qb, k), offsets, k, metric)
+    Do = torch.empty((world * Qb, k), dtype=Dm.dtype, device=Dm.device)
+    Io = torch.empty((world * Qb, k), dtype=Im.dtype, device=Im.device)
+    dist.all_gather_into_tensor(Do, Dm.contiguous(), group=group)
+    dist.all_gather_into_tensor(Io, Im.contiguous(), group=group)
     return Do[:Q], Io[:Q]
 
 

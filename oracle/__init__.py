@@ -20,6 +20,7 @@ from .flat_search import (  # noqa: F401
     numpy_ip_search,
     reference_chunked_search,
     blocked_ip_search,
+    blocked_ip_search_thr,
     blocked_l2_search,
     faiss_pad,
     exact_scores_f64,

@@ -441,3 +441,46 @@ def test_tensor_kernel_two_sets_fallback(k1_sets):
     hot = np.flatnonzero((np.arange(n) // 256) % 16 == 0)      # every row that matters lies in a sample tile: the fall-back must run
     c[hot] += x[rng.integers(0, q, size=hot.size)] * rng.uniform(0.5, 1.0, size=(hot.size, 1)).astype(np.float32)
     run_and_check(c, x, k, store="bf16", path="tensor", rtol=1e-5, expect_path="tensor", min_recall=0.999)
+
+
+def test_two_streams_one_handle_no_caller_sync():
+    """SURVEY.md 8(b) "concurrent search on distinct streams": one handle, two non-blocking streams, interleaved device-in /
+    device-out searches of different shapes (K1 and K2T carve the shared scratch arena differently) with no synchronisation by the
+    caller between them.  The library orders the calls on the device (include/nexus_flat.h "Thread-safety and streams"); every
+    result is compared with the oracle."""
+    import torch
+    from nexus_b200 import FlatIndex
+    c, xa = gen_inputs(60000, 128, 300, seed=77)
+    _, xb = gen_inputs(8, 128, 16, seed=78)
+    idx = FlatIndex(128, "ip", "bf16")
+    idx.add(c)
+    cs = oracle.round_to_bf16(c)
+    ref_a = oracle.blocked_ip_search(cs, xa, 50)
+    ref_b = oracle.blocked_ip_search(cs, xb, 10)
+    qa, qb = torch.from_numpy(xa).cuda(), torch.from_numpy(xb).cuda()
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    torch.cuda.synchronize()
+    outs = []
+    for it in range(50):
+        with torch.cuda.stream(sa):
+            Da, Ia = idx.search(qa, 50)
+        with torch.cuda.stream(sb):
+            Db, Ib = idx.search(qb, 10)
+        outs.append((Da, Ia, Db, Ib))
+    torch.cuda.synchronize()
+    for Da, Ia, Db, Ib in outs:
+        rep = oracle.check_topk(ref_a[0], ref_a[1], Da.cpu().numpy(), Ia.cpu().numpy(), cs, xa)
+        assert rep.ok, rep.messages[:5]
+        rep = oracle.check_topk(ref_b[0], ref_b[1], Db.cpu().numpy(), Ib.cpu().numpy(), cs, xb)
+        assert rep.ok, rep.messages[:5]
+    # add on one stream, search on another, no sync: the search must see the converted rows
+    idx2 = FlatIndex(128, "ip", "bf16")
+    ct = torch.from_numpy(c).cuda()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(sa):
+        idx2.add(ct)
+    with torch.cuda.stream(sb):
+        D2, I2 = idx2.search(qa, 50)
+    torch.cuda.synchronize()
+    rep = oracle.check_topk(ref_a[0], ref_a[1], D2.cpu().numpy(), I2.cpu().numpy(), cs, xa)
+    assert rep.ok, rep.messages[:5]

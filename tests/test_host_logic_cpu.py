@@ -41,8 +41,10 @@ def test_row_views():
     b = _as_rows(np.zeros(4, np.float32), 4, "t")
     assert b.n == 1
     t = torch.zeros(5, 8, dtype=torch.bfloat16)
-    b = _as_rows(t[:, :4], None, "t")          # strided view keeps its row stride
-    assert b.dtype == L.BF16 and b.ld == 8 and b.d == 4
+    b = _as_rows(t[:, :4], None, "t")          # a strided HOST view is densified: the host paths copy n*ld contiguous elements,
+    assert b.dtype == L.BF16 and b.ld == 4 and b.d == 4   # which would run past the storage on the last row
+    b = _as_rows(t[:, 4:], None, "t")
+    assert b.ld == 4 and b.keep.is_contiguous()
     with pytest.raises(ValueError):
         _as_rows(a, 5, "t")
     with pytest.raises(ValueError):
