@@ -2,6 +2,7 @@
 with the direct restatement of NumpyIPIndex whatever the block sizes, and the MMEB local ranking must be the global ranking
 restricted to the query's own list.  Continuous random inputs: no exact ties, so ids are compared exactly."""
 import numpy as np
+import pytest
 from hypothesis import given, settings, strategies as st
 
 import oracle
@@ -50,3 +51,14 @@ def test_mmeb_local_ranking_is_the_global_ranking_restricted_to_the_list(nc, d, 
             a = np.array([scores[qi][keys.index(n)] for n in got])
             b = np.array([scores[qi][keys.index(n)] for n in expect])
             np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("n,d,q,k,block", [(5000, 32, 50, 10, 512), (70000, 48, 33, 100, 8192), (300, 16, 7, 500, 64), (20000, 24, 9, 1, 4096)])
+def test_threshold_filtered_search_equals_blocked_search(n, d, q, k, block):
+    """The timed CPU baseline (bench.py) uses blocked_ip_search_thr: same products, same results as blocked_ip_search."""
+    c = oracle.make_unit_gaussian(n, d, seed=n % 97)
+    x = oracle.make_unit_gaussian(q, d, seed=q)
+    a = oracle.blocked_ip_search(c, x, k, block_rows=block)
+    b = oracle.blocked_ip_search_thr(c, x, k, block_rows=block)
+    np.testing.assert_array_equal(a[1], b[1])
+    np.testing.assert_array_equal(a[0], b[0])
