@@ -22,7 +22,8 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
   __shared__ uint32_t hist[256];
   __shared__ uint32_t sh_prefix;
   __shared__ int sh_need, sh_gt, sh_eq;
-  __shared__ float sh_qnorm;
+  __shared__ float sh_qnorm, sh_tau_min;
+  __shared__ float red[mg::THREADS / 32];
 
   const int64_t qi = blockIdx.x;
   const int tid = threadIdx.x;
@@ -41,8 +42,7 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
       q_s[d] = v;
       part += v * v;
     }
-    // block reduce |q|^2 (only the L2 output needs it)
-    __shared__ float red[mg::THREADS / 32];
+    // block reduce |q|^2 (the L2 output and the certificate need it)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(kFullMask, part, o);
     if ((tid & 31) == 0) red[tid >> 5] = part;
@@ -75,6 +75,22 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
     for (int i = tid; i < M; i += mg::THREADS) ent[i] = src[i];
   }
   __syncthreads();
+
+  // ---- certificate, first half: tau' = the smallest PASS score among the kept candidates bounds the pass score of every other row ----
+  if (p.cert) {
+    float mn = INFINITY;
+    for (int i = tid; i < keep; i += mg::THREADS) mn = fminf(mn, ent[i].score);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(kFullMask, mn, o));
+    __syncthreads();  // red[] is free again (|q|^2 was folded before the previous barrier)
+    if ((tid & 31) == 0) red[tid >> 5] = mn;
+    __syncthreads();
+    if (tid == 0) {
+      float m = red[0];
+      for (int w = 1; w < mg::THREADS / 32; ++w) m = fminf(m, red[w]);
+      sh_tau_min = m;
+    }
+  }
 
   // ---- exact fp32 re-score: one warp per candidate, two candidates in flight per warp, 16-byte loads ----
   // (rows are ld = 64k elements long and zero padded, q_s holds ld entries: no tail handling)
@@ -123,6 +139,19 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
     keys[i] = kk;
   }
   block_bitonic_desc<false>(keys, nullptr, P);
+
+  // ---- certificate, second half: the re-scored k-th score must clear tau' + eps (params.cuh, MergeArenaParams::cert) ----
+  if (p.cert && tid == 0) {
+    bool pass = static_cast<int64_t>(keep) >= p.n_rows;     // every row of the index was a candidate
+    if (!pass && keep >= p.k_out) {
+      const float s_k = sort_key_score(keys[p.k_out - 1]);
+      const float mx = __uint_as_float(*p.max_norm2);
+      const float eps = (p.eps_rel * sqrtf(sh_qnorm) + p.eps_abs) * sqrtf(mx) * 1.0001f;
+      pass = s_k >= sh_tau_min + eps;
+    }
+    p.cert_fail[qi] = pass ? 0u : 1u;
+    if (!pass) atomicAdd(p.cert_count, 1u);
+  }
 
   const float qn = (p.metric == NXF_METRIC_L2) ? sh_qnorm : 0.f;
   for (int j = tid; j < p.k_out; j += mg::THREADS) {

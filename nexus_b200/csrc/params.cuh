@@ -61,9 +61,11 @@ __device__ __forceinline__ int64_t perm_tile(const TilePerm& tp, int64_t v64) {
 struct K1Params {
   int64_t n;    // corpus rows
   int64_t nq;   // query rows
-  int kblocks;  // K blocks of 64 elements accumulated per tile: ld / 64, or 3 * split_kb
-  int split_kb; // 0, or (fp32 storage as two bf16 planes [hi | mid] per row, each split_kb blocks wide) the plane width: the three
-                // segments of a tile are (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
+  int kblocks;  // K blocks of 64 elements accumulated per tile: ld / 64, or (segmented) segments * split_kb
+  int split_kb; // 0, or the plane width in K blocks of a segmented search (the retry level of the certified search):
+                // the queries are two bf16 planes [hi | mid] per row (hi = bf16(x), mid = bf16(x - hi)) and a tile accumulates
+  int seg_mode; //   1 (fp32 storage: corpus planes hi = tmap_c, mid = tmap_c2): (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
+                //   2 (16-bit storage, one corpus plane):                       (q_hi, c), (q_mid, c)
   int num_qt;   // query tiles of 128*CG rows (<= number of clusters)
   int epi_sets; // 1 or 2 epilogue warp sets (set s filters accumulator buffer s); 2 when a tile holds too few K blocks to hide one set
   int64_t tile_begin, tile_end;  // (virtual) corpus tiles [begin, end) of this pass (a search is 1-3 passes: sample, sample, rest)
@@ -98,8 +100,7 @@ struct K2TParams {
   int64_t n;     // corpus rows
   int nq;        // queries (<= 128)
   int nq_pad;    // nq rounded up to 16 = UMMA N
-  int kblocks;   // 64-element K blocks per row (queries and corpus alike): ld / 64, or 2 * split_kb
-  int split_kb;  // 0, or (fp32 storage as bf16 planes [hi | mid]) blocks per plane: a c_hi block meets q_hi and q_mid, a c_mid block q_hi
+  int kblocks;   // 64-element K blocks per row (queries and corpus alike): ld / 64
   int stages;    // ring depth
   int tbufs;     // TMEM accumulator buffers
   int tbuf_stride;  // TMEM columns between buffers
@@ -127,6 +128,15 @@ struct MergeArenaParams {
   int k_out;    // columns of the output
   int metric;   // NXF_METRIC_*
   int rescore;  // recompute the kept candidates' scores in fp32 from q and the stored rows
+  // certificate of the candidate pass (DESIGN.md "certified search"): every row NOT among the kept k' has a pass score <= tau' (the
+  // smallest kept pass score), hence a true score <= tau' + eps with eps = eps_rel * |q| * max|c| (+ eps_abs * max|c|); the re-scored
+  // top-k is exact iff its k-th true score >= tau' + eps.  Queries that fail are flagged for the retry level.
+  int cert;                   // evaluate it (needs rescore)
+  float eps_rel, eps_abs;
+  const uint32_t* max_norm2;  // device word: float bits of max over stored rows of |row|^2
+  int64_t n_rows;             // rows in the index (a query that kept them all passes)
+  uint32_t* cert_fail;        // [nq] 1 = failed
+  uint32_t* cert_count;       // [1] number of failed queries (atomicAdd)
   const float* q;  // [nq, ldq] fp32 (needed when rescore or metric == L2)
   int64_t ldq;
   const void* corpus;
@@ -172,12 +182,13 @@ struct MergeListsParams {
 };
 
 int launch_kx(int store_dtype, const KxParams& p, int grid, cudaStream_t stream);
-int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, const void* corpus, int64_t ld, const K1Params& p,
-              int grid, cudaStream_t stream);
+// q16: [nq_rows, q_ld] 16-bit queries; corpus: [n, ld] 16-bit rows; corpus2 (seg_mode 1 only): the mid plane, same shape
+int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, int64_t q_ld, const void* corpus, const void* corpus2,
+              int64_t ld, const K1Params& p, int grid, cudaStream_t stream);
 int k1_smem_bytes(int cta_group);
 int launch_k2(int store_dtype, const K2Params& p, int nq_t, int rw, int grid, size_t smem, cudaStream_t stream);
 size_t k2_smem_bytes(int64_t ld, int elem_size, int nq_t, int rw, int stages);
-int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* corpus, int64_t ld, const K2TParams& p, int grid,
+int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, int64_t q_ld, const void* corpus, int64_t ld, const K2TParams& p, int grid,
                cudaStream_t stream);
 size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages);
 int k2t_plan_stages(int kblocks, int nq_pad);
@@ -193,6 +204,11 @@ int launch_positive_rank(const float* pos, const float* topk, int64_t nq, int k,
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,
                         cudaStream_t stream);
 int launch_split_rows(const float* src, int64_t ld, void* dst, int64_t n, cudaStream_t stream);
+int launch_mid_rows(const float* src, int64_t ld, void* dst, int64_t n, cudaStream_t stream);
+int launch_row_norm_max(const void* rows, int dtype, int64_t ld, int64_t n, int dim, uint32_t* max_norm2, cudaStream_t stream);
+int launch_gather_rows(const void* src, int64_t row_bytes, const int64_t* rows, int64_t n, void* dst, cudaStream_t stream);
+int launch_scatter_results(const float* src_scores, const int64_t* src_ids, const Entry* src_packed, const int64_t* rows, int64_t n, int k,
+                           float* dst_scores, int64_t* dst_ids, Entry* dst_packed, cudaStream_t stream);
 int launch_half_norm(const void* rows, int dtype, int64_t ld, int64_t n, int dim, float* out, cudaStream_t stream);
 int launch_pool(const void* hidden, int h_dtype, const int64_t* mask, int64_t B, int64_t L, int64_t H, int pooling, int normalize,
                 float eps, void* out, int out_dtype, cudaStream_t stream);

@@ -215,17 +215,10 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         tc_fence_after();
         if (lane == 0) {
           const uint64_t a_desc = a_desc0 + static_cast<uint32_t>(s) * static_cast<uint32_t>(A_BYTES >> 4);
-          // split storage: corpus block kb of the hi plane meets q_hi[kb] and q_mid[kb]; of the mid plane, q_hi[kb - split_kb]
-          const int qb = (p.split_kb > 0 && kb >= p.split_kb) ? kb - p.split_kb : kb;
-          const uint64_t b_desc = b_desc0 + static_cast<uint32_t>(qb) * q_blk;
+          const uint64_t b_desc = b_desc0 + static_cast<uint32_t>(kb) * q_blk;
           umma_f16<1>(d_tmem, a_desc, b_desc, idesc, kb != 0 ? 1u : 0u);
 #pragma unroll
           for (int k4 = 1; k4 < BLOCK_K / UMMA_K; ++k4) umma_f16<1>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, 1u);
-          if (p.split_kb > 0 && kb < p.split_kb) {
-            const uint64_t b2_desc = b_desc0 + static_cast<uint32_t>(kb + p.split_kb) * q_blk;
-#pragma unroll
-            for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) umma_f16<1>(d_tmem, a_desc + 2 * k4, b2_desc + 2 * k4, idesc, 1u);
-          }
           umma_commit<1>(&empty[s]);
           if (kb == p.kblocks - 1) umma_commit<1>(&tfull[b]);
         }
@@ -370,12 +363,12 @@ int k2t_plan_stages(int kblocks, int nq_pad) {
   return 0;
 }
 
-int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, const void* corpus, int64_t ld, const K2TParams& p, int grid,
+int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, int64_t q_ld, const void* corpus, int64_t ld, const K2TParams& p, int grid,
                cudaStream_t stream) {
   const bool bf16 = store_dtype == NXF_BF16;
   if (store_dtype != NXF_BF16 && store_dtype != NXF_F16) { set_error("tensor stream search needs f16/bf16 storage"); return NXF_EUNSUPPORTED; }
   CUtensorMap tq, tc;
-  int rc = make_tmap_2d_sw128(&tq, q16, nq_rows, ld, p.nq_pad, bf16);
+  int rc = make_tmap_2d_sw128(&tq, q16, nq_rows, q_ld, p.nq_pad, bf16);
   if (rc) return rc;
   rc = make_tmap_2d_sw128(&tc, corpus, p.n, ld, k2t::BLOCK_M, bf16);
   if (rc) return rc;

@@ -159,7 +159,8 @@ __device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0,
 // per-row thresholds, counters and candidate buffers -- to the rest of the search it is one more owner of the query.
 template <int CG, bool BF16, int SETS>
 __global__ void __launch_bounds__(128 + 128 * SETS, 1)
-k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K1Params p) {
+k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
+                 const __grid_constant__ CUtensorMap tmap_c2, K1Params p) {
   using namespace k1;
   using C = Cfg<CG>;
   extern __shared__ unsigned char smem_raw[];
@@ -182,6 +183,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
     tma_prefetch_desc(&tmap_c);
+    if (p.seg_mode == 1) tma_prefetch_desc(&tmap_c2);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full[s], CG); mbar_init(&empty[s], 1); }
@@ -218,12 +220,20 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           for (int64_t t = r0 + lo; t < r0 + hi; ++t) {
             const int32_t c_row0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_N + rank * C::LOAD_N);
             for (int kb = 0; kb < p.kblocks; ++kb) {
-              // column (in elements) of this K block in the query / corpus rows; split storage walks (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi)
+              // column (in elements) of this K block in the query / corpus rows.  Segmented search (K1Params::seg_mode): the query
+              // planes are [hi | mid] in one row; mode 1 walks (q_hi, c_hi), (q_hi, c_mid), (q_mid, c_hi) with the corpus mid plane behind
+              // its own tensor map, mode 2 walks (q_hi, c), (q_mid, c)
               int32_t q_col = kb * BLOCK_K, c_col = kb * BLOCK_K;
+              const CUtensorMap* cm = &tmap_c;
               if (p.split_kb > 0) {
                 const int seg = kb / p.split_kb, w = kb - seg * p.split_kb;
-                q_col = ((seg == 2 ? p.split_kb : 0) + w) * BLOCK_K;
-                c_col = ((seg == 1 ? p.split_kb : 0) + w) * BLOCK_K;
+                c_col = w * BLOCK_K;
+                if (p.seg_mode == 1) {
+                  q_col = ((seg == 2 ? p.split_kb : 0) + w) * BLOCK_K;
+                  if (seg == 1) cm = &tmap_c2;
+                } else {
+                  q_col = (seg * p.split_kb + w) * BLOCK_K;
+                }
               }
               mbar_wait(&empty[s], ph ^ 1);
               if (p.debug & 4) {  // pipeline timing only: no loads, the MMAs run on whatever the ring holds
@@ -231,10 +241,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               } else if (CG == 1) {
                 mbar_expect_tx(&full[s], C::STAGE_BYTES);
                 tma_load_2d(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
-                tma_load_2d(&tmap_c, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
+                tma_load_2d(cm, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
               } else {
                 tma_load_2d_2sm(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
-                tma_load_2d_2sm(&tmap_c, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
+                tma_load_2d_2sm(cm, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
                 if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
                 else mbar_arrive_cluster(&full[s], 0);
               }
@@ -512,7 +522,7 @@ static int encode_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, 
 }
 
 template <int CG, bool BF16, int SETS>
-static int launch_k1_t(const CUtensorMap& tq, const CUtensorMap& tc, const K1Params& p, int grid, cudaStream_t stream) {
+static int launch_k1_t(const CUtensorMap& tq, const CUtensorMap& tc, const CUtensorMap& tc2, const K1Params& p, int grid, cudaStream_t stream) {
   using C = k1::Cfg<CG>;
   auto kern = k1_search_kernel<CG, BF16, SETS>;
   if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), C::SMEM_BYTES)) return rc;
@@ -528,26 +538,33 @@ static int launch_k1_t(const CUtensorMap& tq, const CUtensorMap& tc, const K1Par
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  NXF_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tc, p));
+  NXF_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tc, tc2, p));
   return NXF_OK;
 }
 
-// q16: [nq_rows, ld] 16-bit queries (device), corpus: [n, ld] 16-bit rows (device)
-int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, const void* corpus, int64_t ld, const K1Params& p,
-              int grid, cudaStream_t stream) {
+// q16: [nq_rows, q_ld] 16-bit queries (device), corpus (and corpus2, the mid plane of a mode-1 segmented search): [n, ld] 16-bit rows
+int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, int64_t q_ld, const void* corpus, const void* corpus2,
+              int64_t ld, const K1Params& p, int grid, cudaStream_t stream) {
   const bool bf16 = store_dtype == NXF_BF16;
   if (store_dtype != NXF_BF16 && store_dtype != NXF_F16) { set_error("tensor-core search needs f16/bf16 storage"); return NXF_EUNSUPPORTED; }
-  CUtensorMap tq, tc;
-  int rc = make_tmap_2d_sw128(&tq, q16, nq_rows, ld, k1::BLOCK_M, bf16);
+  if (p.seg_mode == 1 && corpus2 == nullptr) { set_error("launch_k1: segmented search over fp32 storage needs the mid plane"); return NXF_EINVAL; }
+  CUtensorMap tq, tc, tc2;
+  int rc = make_tmap_2d_sw128(&tq, q16, nq_rows, q_ld, k1::BLOCK_M, bf16);
   if (rc) return rc;
   rc = make_tmap_2d_sw128(&tc, corpus, p.n, ld, k1::BLOCK_N / cta_group, bf16);
   if (rc) return rc;
-  if (p.epi_sets == 2) {
-    if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 2>(tq, tc, p, grid, stream) : launch_k1_t<2, false, 2>(tq, tc, p, grid, stream);
-    return bf16 ? launch_k1_t<1, true, 2>(tq, tc, p, grid, stream) : launch_k1_t<1, false, 2>(tq, tc, p, grid, stream);
+  if (p.seg_mode == 1) {
+    rc = make_tmap_2d_sw128(&tc2, corpus2, p.n, ld, k1::BLOCK_N / cta_group, bf16);
+    if (rc) return rc;
+  } else {
+    tc2 = tc;
   }
-  if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 1>(tq, tc, p, grid, stream) : launch_k1_t<2, false, 1>(tq, tc, p, grid, stream);
-  return bf16 ? launch_k1_t<1, true, 1>(tq, tc, p, grid, stream) : launch_k1_t<1, false, 1>(tq, tc, p, grid, stream);
+  if (p.epi_sets == 2) {
+    if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 2>(tq, tc, tc2, p, grid, stream) : launch_k1_t<2, false, 2>(tq, tc, tc2, p, grid, stream);
+    return bf16 ? launch_k1_t<1, true, 2>(tq, tc, tc2, p, grid, stream) : launch_k1_t<1, false, 2>(tq, tc, tc2, p, grid, stream);
+  }
+  if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 1>(tq, tc, tc2, p, grid, stream) : launch_k1_t<2, false, 1>(tq, tc, tc2, p, grid, stream);
+  return bf16 ? launch_k1_t<1, true, 1>(tq, tc, tc2, p, grid, stream) : launch_k1_t<1, false, 1>(tq, tc, tc2, p, grid, stream);
 }
 
 int k1_smem_bytes(int cta_group) { return cta_group == 2 ? k1::Cfg<2>::SMEM_BYTES : k1::Cfg<1>::SMEM_BYTES; }
