@@ -119,6 +119,11 @@ typedef struct nxf_stats {
   int64_t storage_bytes;   /* device bytes of row storage currently held */
   int64_t main_kernel_count; /* main search kernels timed since nxf_set_profiling(idx, 1) */
   double main_kernel_ms;     /* their summed device time (CUDA events on the launching stream) */
+  /* certified search (see nxf_search): queries whose candidate pass was checked, and how many of them were searched again by the
+   * segmented tensor-core pass (level 2) and by the exact fp32 kernels (level 3) because their certificate failed */
+  int64_t cert_checked;
+  int64_t cert_retry_l2;
+  int64_t cert_retry_l3;
 } nxf_stats;
 
 /* ---- library ---- */
@@ -171,7 +176,17 @@ NXF_API int nxf_reconstruct(nxf_index* idx, int64_t first, int64_t n, float* dst
 /* ---- search ---- */
 /* q: nq x dim of q_dtype, row stride q_ld elements (0 = dim), host or device (q_on_device).
  * out_scores [nq,k] float32 and out_ids [nq,k] int64, caller-allocated, both host or both device
- * (out_on_device).  1 <= k <= NXF_MAX_K.  flags: NXF_SEARCH_*. */
+ * (out_on_device).  1 <= k <= NXF_MAX_K.  flags: NXF_SEARCH_*.
+ *
+ * Exactness.  The reference arithmetic is plain fp32 (utils.py:21-22,224).  The tensor-core kernels see 16-bit operands, so unless
+ * the queries already are of the index's 16-bit storage type a search is CERTIFIED: the candidate pass keeps k' > k rows per query
+ * (2k for 16-bit storage: only the query is rounded, every pass score is within 2^-9 |q||c| of the fp32 score; 4k for fp32 storage,
+ * which streams a bf16 copy of its rows: 2^-8 |q||c|), the candidates are re-scored with fp32 FMAs on the stored rows, and the
+ * result of a query stands only if its k-th re-scored score clears the smallest kept pass score by that bound -- then no row
+ * outside the candidates can belong to the top-k.  A query that fails is searched again by a segmented tensor-core pass whose
+ * products reproduce the fp32 ones to ~1e-4 |q||c| (same certificate), and, failing that too, by the exact fp32 FMA kernels.
+ * The certificate costs one 4-byte read-back per call: a certified search drains `stream` before it returns, device buffers or
+ * not.  NXF_SEARCH_NO_RESCORE switches re-score and certificate off (raw tensor-core scores); the counters are in nxf_stats. */
 NXF_API int nxf_search(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld,
                        int q_on_device, int k, float* out_scores, int64_t* out_ids, int out_on_device,
                        int flags, void* stream);

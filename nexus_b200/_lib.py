@@ -45,6 +45,7 @@ class Stats(C.Structure):
         ("last_path", C.c_int32), ("last_k_fetch", C.c_int32), ("last_chunks", C.c_int32), ("last_grid", C.c_int32),
         ("scratch_bytes", C.c_int64), ("storage_bytes", C.c_int64),
         ("main_kernel_count", C.c_int64), ("main_kernel_ms", C.c_double),
+        ("cert_checked", C.c_int64), ("cert_retry_l2", C.c_int64), ("cert_retry_l3", C.c_int64),
     ]
 
 

@@ -62,10 +62,12 @@ struct nxf_index {
   int64_t n = 0, capacity = 0;
   void* data = nullptr;    // [capacity, ld] of store_dtype
   float* half_norm = nullptr;  // [capacity] 0.5*|row|^2 (L2 only)
-  // fp32 storage only: the rows again as two bf16 planes [hi | mid] per row, the operand of the tensor-core path (built on first use)
-  void* split = nullptr;       // [split_cap + 256, 2 * ld] bf16
-  int64_t split_cap = 0, split_rows = 0;  // rows allocated / rows converted so far
-  bool split_failed = false;   // the shadow did not fit in device memory: stay on the FFMA kernel until the storage changes
+  // fp32 storage only: the bf16 operand planes of the tensor-core path (DESIGN.md "certified search"), built on first use
+  void* hi = nullptr;          // [hi_cap + 256, ld] bf16(x): the candidate pass streams this plane alone (2 bytes per element)
+  void* mid = nullptr;         // [mid_cap + 256, ld] bf16(x - hi): built only when a query fails its certificate (retry level)
+  int64_t hi_cap = 0, hi_rows = 0, mid_cap = 0, mid_rows = 0;  // rows allocated / rows converted so far
+  bool hi_failed = false, mid_failed = false;  // the plane did not fit in device memory (until the storage changes)
+  uint32_t* max_norm2 = nullptr;  // device word: float bits of max |stored row|^2, raised by every add (the certificate's |c| bound)
   int64_t id_offset = 0;
   int sm_count = 0;
   int cc_major = 0;
@@ -161,8 +163,11 @@ int ensure_capacity(nxf_index* idx, int64_t want, cudaStream_t stream) {
   }
   if (idx->data) cudaFree(idx->data);
   if (idx->half_norm) cudaFree(idx->half_norm);
-  if (idx->split) cudaFree(idx->split);
-  idx->split = nullptr; idx->split_cap = 0; idx->split_rows = 0; idx->split_failed = false;
+  if (idx->hi) cudaFree(idx->hi);
+  if (idx->mid) cudaFree(idx->mid);
+  idx->hi = idx->mid = nullptr;
+  idx->hi_cap = idx->hi_rows = idx->mid_cap = idx->mid_rows = 0;
+  idx->hi_failed = idx->mid_failed = false;
   idx->data = nd;
   idx->half_norm = nh;
   idx->capacity = cap;
@@ -170,30 +175,35 @@ int ensure_capacity(nxf_index* idx, int64_t want, cudaStream_t stream) {
   return NXF_OK;
 }
 
-// fp32 storage: bring the two-plane bf16 shadow up to date with the stored rows.  Returns NXF_ENOMEM (and remembers it) when the
-// shadow does not fit; the caller then stays on the FFMA kernel.
-int ensure_split(nxf_index* idx, cudaStream_t stream) {
-  if (idx->split_failed) return NXF_ENOMEM;
-  if (idx->split_cap < idx->capacity) {
-    if (idx->split) { cudaFree(idx->split); idx->split = nullptr; idx->split_cap = 0; idx->split_rows = 0; }
-    const size_t bytes = static_cast<size_t>(idx->capacity + 256) * idx->ld * 2 * sizeof(uint16_t);
-    cudaError_t e = cudaMalloc(&idx->split, bytes);
+// fp32 storage: bring a bf16 operand plane (which = 0: hi = bf16(x); 1: mid = bf16(x - hi)) up to date with the stored rows.  Returns
+// NXF_ENOMEM (and remembers it) when the plane does not fit; the caller then stays on / falls back to the FFMA kernels.
+int ensure_plane(nxf_index* idx, int which, cudaStream_t stream) {
+  void*& plane = which ? idx->mid : idx->hi;
+  int64_t& cap = which ? idx->mid_cap : idx->hi_cap;
+  int64_t& rows = which ? idx->mid_rows : idx->hi_rows;
+  bool& failed = which ? idx->mid_failed : idx->hi_failed;
+  if (failed) return NXF_ENOMEM;
+  if (cap < idx->capacity) {
+    if (plane) { cudaFree(plane); plane = nullptr; cap = 0; rows = 0; }
+    const size_t bytes = static_cast<size_t>(idx->capacity + 256) * idx->ld * sizeof(uint16_t);
+    cudaError_t e = cudaMalloc(&plane, bytes);
     if (e != cudaSuccess) {
       cudaGetLastError();
-      idx->split = nullptr;
-      idx->split_failed = true;
+      plane = nullptr;
+      failed = true;
       return NXF_ENOMEM;
     }
-    idx->split_cap = idx->capacity;
+    cap = idx->capacity;
     idx->stats.storage_bytes += static_cast<int64_t>(bytes);
   }
-  if (idx->split_rows < idx->n) {
-    const float* src = static_cast<const float*>(idx->data) + static_cast<size_t>(idx->split_rows) * idx->ld;
-    uint16_t* dst = static_cast<uint16_t*>(idx->split) + static_cast<size_t>(idx->split_rows) * idx->ld * 2;
-    int rc = launch_split_rows(src, idx->ld, dst, idx->n - idx->split_rows, stream);
+  if (rows < idx->n) {
+    const float* src = static_cast<const float*>(idx->data) + static_cast<size_t>(rows) * idx->ld;
+    uint16_t* dst = static_cast<uint16_t*>(plane) + static_cast<size_t>(rows) * idx->ld;
+    int rc = which ? launch_mid_rows(src, idx->ld, dst, idx->n - rows, stream)
+                   : launch_convert_rows(src, NXF_F32, idx->ld, dst, NXF_BF16, idx->ld, idx->n - rows, static_cast<int>(idx->ld), stream);
     if (rc) return rc;
     idx->stats.kernel_launches++;
-    idx->split_rows = idx->n;
+    rows = idx->n;
   }
   return NXF_OK;
 }
@@ -322,7 +332,9 @@ void nxf_destroy(nxf_index* idx) {
     DeviceGuard g(idx->device);
     if (idx->data) cudaFree(idx->data);
     if (idx->half_norm) cudaFree(idx->half_norm);
-    if (idx->split) cudaFree(idx->split);
+    if (idx->hi) cudaFree(idx->hi);
+    if (idx->mid) cudaFree(idx->mid);
+    if (idx->max_norm2) cudaFree(idx->max_norm2);
     if (idx->scratch) cudaFree(idx->scratch);
     if (idx->pinned) cudaFreeHost(idx->pinned);
     if (idx->last_use) cudaEventDestroy(idx->last_use);
@@ -335,7 +347,7 @@ int nxf_reset(nxf_index* idx) {
   NXF_REQUIRE(idx != nullptr, "nxf_reset: NULL index");
   std::lock_guard<std::mutex> lk(idx->mu);
   idx->n = 0;
-  idx->split_rows = 0;
+  idx->hi_rows = idx->mid_rows = 0;   // max_norm2 stays: a stale (larger) bound only makes the certificate more conservative
   return NXF_OK;
 }
 
@@ -462,6 +474,13 @@ int nxf_add(nxf_index* idx, const void* rows, int64_t n, int src_dtype, int64_t 
     if (rc) return rc;
     idx->stats.kernel_launches++;
   }
+  if (!idx->max_norm2) {
+    NXF_CUDA(cudaMalloc(reinterpret_cast<void**>(&idx->max_norm2), 256));
+    NXF_CUDA(cudaMemsetAsync(idx->max_norm2, 0, 256, stream));
+  }
+  rc = launch_row_norm_max(dst, idx->store_dtype, idx->ld, n, idx->dim, idx->max_norm2, stream);
+  if (rc) return rc;
+  idx->stats.kernel_launches++;
   idx->n += n;
   idx->stats.rows_added += n;
   return NXF_OK;
@@ -524,7 +543,11 @@ struct SearchPlan {
   int k_eff = 0;     // min(k, n)
   int k_fetch = 0;   // per-owner keep count in the main kernel
   int rescore = 0;
-  int split = 0;     // K1 over the two-plane bf16 shadow of fp32 rows
+  int use_hi = 0;    // fp32 storage through its bf16 hi plane (K1 / K2T)
+  int seg_mode = 0;  // K1 retry level: 1 = fp32 storage, three segments over (hi, mid); 2 = 16-bit storage, two query planes
+  int level = 1;     // certified search: 1 candidate pass, 2 segmented retry, 3 exact kernels (no certificate needed)
+  int cert = 0;      // evaluate the certificate in the arena merge
+  float eps_rel = 0.f, eps_abs = 0.f;
   int seed = 0;      // K2T: threshold-seeding pass over the first tile of every CTA
   int cap = 0;
   int epi_sets = 2;
@@ -541,39 +564,47 @@ struct SearchPlan {
   int64_t batch = 0;  // queries per launch
 };
 
+// internal flag bits (above the public NXF_SEARCH_* ones): which level of the certified search this call is
+constexpr int kFlagLevel2 = 1 << 20;
+constexpr int kFlagLevel3 = 1 << 21;
+constexpr int kForceMask = NXF_SEARCH_FORCE_EXACT | NXF_SEARCH_FORCE_STREAM | NXF_SEARCH_FORCE_TENSOR | NXF_SEARCH_FORCE_TSTREAM;
+
+// fp32 accumulation of the tensor cores over `kblocks` K blocks of 64 elements: 4 MMAs per block, two roundings each (the sum of
+// the 16 products, then the add into the accumulator), each taken as <= 1 ulp (2^-23, doubled for a truncating adder) of a
+// partial sum that never exceeds sum|q_i c_i| <= |q||c|
+float acc_slack(int kblocks) { return static_cast<float>(kblocks * 8 + 16) * 2.384185791015625e-07f; }
+
 }  // namespace
 
-static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int flags, bool split_ok, SearchPlan* sp) {
+static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int flags, bool hi_ok, SearchPlan* sp) {
   SearchPlan& P = *sp;
   const bool store16 = idx->store_dtype != NXF_F32;
-  const bool tens = store16 || split_ok;  // K1 can run: 16-bit rows, or fp32 rows with their bf16 shadow
+  const bool tens = store16 || hi_ok;  // K1 / K2T can run: 16-bit rows, or fp32 rows with their bf16 hi plane
   P.k_eff = static_cast<int>(std::min<int64_t>(k, idx->n));
+  P.level = (flags & kFlagLevel3) ? 3 : ((flags & kFlagLevel2) ? 2 : 1);
+  const int64_t row_bytes = idx->ld * dtype_size(idx->store_dtype);
   int path;
-  if (flags & NXF_SEARCH_FORCE_EXACT) path = NXF_PATH_EXACT;
+  if (P.level == 3) path = (nq <= 16) ? NXF_PATH_STREAM : NXF_PATH_EXACT;   // exact fp32 FMAs on the stored values
+  else if (P.level == 2) path = NXF_PATH_TENSOR;                             // segmented K1
+  else if (flags & NXF_SEARCH_FORCE_EXACT) path = NXF_PATH_EXACT;
   else if (flags & NXF_SEARCH_FORCE_STREAM) path = NXF_PATH_STREAM;
   else if (flags & NXF_SEARCH_FORCE_TENSOR) path = NXF_PATH_TENSOR;
   else if (flags & NXF_SEARCH_FORCE_TSTREAM) path = NXF_PATH_TSTREAM;
-  // K2 (CUDA cores, whole-row bulk copies) keeps single queries on long rows, where it already runs at the HBM roofline; short
-  // rows leave most of its lanes idle, so they go to K2T even for one query
-  else if (store16 && nq <= NXF_TSTREAM_MAX_NQ &&
-           nq >= env_int("NXF_TSTREAM_MIN_NQ", idx->ld * dtype_size(idx->store_dtype) < 512 ? 1 : 2))
-    path = NXF_PATH_TSTREAM;
-  // fp32 rows: K2 keeps up with HBM for one query (78 % at two); from two on the shadow planes go through K2T
-  else if (split_ok && nq <= NXF_TSTREAM_MAX_NQ && nq >= env_int("NXF_TSTREAM_MIN_NQ_F32", 2))
-    path = NXF_PATH_TSTREAM;
+  // small batches stream the corpus once through the tensor cores (K2T); round 2: also a single query on long rows (same GB/s as
+  // K2 there, and a tenth of its arena to merge) and fp32 storage, which streams its 2-byte hi plane instead of the 4-byte rows
+  else if (store16 && nq <= NXF_TSTREAM_MAX_NQ && nq >= env_int("NXF_TSTREAM_MIN_NQ", 1)) path = NXF_PATH_TSTREAM;
+  else if (hi_ok && nq <= NXF_TSTREAM_MAX_NQ && nq >= env_int("NXF_TSTREAM_MIN_NQ_F32", 1)) path = NXF_PATH_TSTREAM;
   else if (nq <= NXF_STREAM_MAX_NQ) path = NXF_PATH_STREAM;
   else path = tens ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
 
-  const int64_t row_bytes = idx->ld * dtype_size(idx->store_dtype);
   if (path == NXF_PATH_TSTREAM) {
-    // K2T keeps the (16-padded) queries resident in shared memory; if that leaves fewer than 4 ring stages, or the storage is
-    // fp32, fall back to the kernels that do not need it
+    // K2T keeps the (16-padded) queries resident in shared memory; if that leaves fewer than 4 ring stages fall back to the kernels
+    // that do not need it
     const int nq_pad = static_cast<int>(round_up64(std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ), 16));
-    const int st = store16 ? k2t_plan_stages(static_cast<int>(idx->ld / 64), nq_pad)
-                           : (split_ok ? k2t_plan_stages(static_cast<int>(2 * idx->ld / 64), nq_pad) : 0);
+    const int st = tens ? k2t_plan_stages(static_cast<int>(idx->ld / 64), nq_pad) : 0;
     if (st == 0) {
       if (flags & NXF_SEARCH_FORCE_TSTREAM) {
-        set_error("nxf_search: the tensor stream kernel needs queries that fit in shared memory (nq=%lld, dim=%d) and, for f32 storage, the bf16 shadow",
+        set_error("nxf_search: the tensor stream kernel needs queries that fit in shared memory (nq=%lld, dim=%d) and, for f32 storage, the bf16 plane",
                   (long long)nq, idx->dim);
         return NXF_EUNSUPPORTED;
       }
@@ -592,20 +623,55 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     while (stages > 1 && k2_smem_bytes(idx->ld, dtype_size(idx->store_dtype), nq_t, rw, stages) > 200 * 1024) --stages;
     if (stages < 2) {
       if (flags & NXF_SEARCH_FORCE_STREAM) { set_error("nxf_search: rows of %lld bytes are too long for the stream kernel", (long long)row_bytes); return NXF_EUNSUPPORTED; }
-      path = tens ? NXF_PATH_TENSOR : NXF_PATH_EXACT;
+      path = (P.level == 3 || !tens) ? NXF_PATH_EXACT : NXF_PATH_TENSOR;
     } else {
       P.rw = rw; P.nq_t = nq_t; P.stages = stages;
       P.k2_smem = k2_smem_bytes(idx->ld, dtype_size(idx->store_dtype), nq_t, rw, stages);
     }
   }
   if (path == NXF_PATH_TENSOR && !tens) {
-    set_error("nxf_search: the tensor-core path over f32 storage needs its bf16 shadow, which did not fit in device memory (or NXF_F32_TENSOR=0)");
+    set_error("nxf_search: the tensor-core path over f32 storage needs its bf16 plane, which did not fit in device memory (or NXF_F32_TENSOR=0)");
     return NXF_EUNSUPPORTED;
   }
   P.path = path;
-  P.split = ((path == NXF_PATH_TENSOR || path == NXF_PATH_TSTREAM) && !store16) ? 1 : 0;
+  const bool tpath = path == NXF_PATH_TENSOR || path == NXF_PATH_TSTREAM;
+  P.use_hi = (tpath && !store16) ? 1 : 0;
   P.k_fetch = P.k_eff;
   P.rescore = 0;
+  // ---- certified search: the MMA sees queries (and, for fp32 storage, rows) rounded to 16 bits.  Unless the caller's
+  // queries already are of the storage type, over-fetch k' candidates, re-score them in fp32 and certify the result ----
+  const bool q_exact = store16 && q_dtype == idx->store_dtype;
+  if (tpath && !(flags & NXF_SEARCH_NO_RESCORE) && !q_exact) {
+    P.rescore = 1;
+    const int kb = static_cast<int>(idx->ld / 64);
+    int64_t kf;
+    if (P.level == 2) {
+      // segmented retry: the pass score is within ~1e-4 |q||c| of the fp32 score, a quarter more candidates is plenty
+      kf = static_cast<int64_t>(P.k_eff) + std::max<int64_t>(16, (P.k_eff + 3) / 4);
+      P.seg_mode = store16 ? 2 : 1;
+      if (path != NXF_PATH_TENSOR) P.seg_mode = 0;
+      P.eps_rel = (store16 ? 7.62939453125e-06f : 3.f * 7.62939453125e-06f) + acc_slack(kb * (store16 ? 2 : 3));   // 2^-17, 3 * 2^-17
+    } else if (store16) {
+      // query rounding only: |q - q16| <= 2^-9 |q| -> every pass score within 2^-9 |q||c| of the fp32 score; k' = 2k keeps the gap
+      // between ranks k and k' above that on the BASELINE configs (C2: 0.0069 against 0.0020)
+      kf = std::max<int64_t>(static_cast<int64_t>(std::max(1, env_int("NXF_KFETCH_MULT16", 2))) * P.k_eff, P.k_eff + 16);
+      P.eps_rel = 0.001953125f + acc_slack(kb);
+    } else {
+      // fp32 rows through their bf16 hi plane: both operands rounded, (2^-8 + 2^-16) |q||c|; k' = 4k
+      kf = std::max<int64_t>(static_cast<int64_t>(std::max(1, env_int("NXF_KFETCH_MULT32", 4))) * P.k_eff, P.k_eff + 64);
+      P.eps_rel = 0.00390625f + 1.52587890625e-05f + acc_slack(kb);
+    }
+    if (idx->store_dtype == NXF_F16) P.eps_abs = std::sqrt(static_cast<float>(idx->dim)) * 5.9604644775390625e-08f;  // f16 subnormals: 2^-24 per element
+    kf = (kf + 7) / 8 * 8;
+    P.k_fetch = static_cast<int>(std::max<int64_t>(P.k_eff, std::min<int64_t>(std::min<int64_t>(kf, NXF_MAX_K), idx->n)));
+    P.cert = env_int("NXF_CERT", 1) != 0 ? 1 : 0;
+    if (!P.cert && P.level == 1) {
+      // NXF_CERT=0: round 1's fixed over-fetch k' = k + max(16, k/4), no certificate, no retry (kept for A/B timing)
+      int64_t k1 = static_cast<int64_t>(P.k_eff) + std::max<int64_t>(16, (P.k_eff + 3) / 4);
+      k1 = (k1 + 7) / 8 * 8;
+      P.k_fetch = static_cast<int>(std::max<int64_t>(P.k_eff, std::min<int64_t>(std::min<int64_t>(k1, NXF_MAX_K), idx->n)));
+    }
+  }
   if (path == NXF_PATH_STREAM) {
     const int64_t R = 8 * P.rw;
     const int64_t n_blocks = ceil_div64(idx->n, R);
@@ -615,17 +681,10 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     P.arena_stride = static_cast<int64_t>(P.grid) * 8 * P.k_eff;
     P.batch = P.nq_t;
   } else if (path == NXF_PATH_TSTREAM) {
-    // same query-side rounding as K1: over-fetch and re-score in fp32 unless the queries already are of the storage type
-    if (!(flags & NXF_SEARCH_NO_RESCORE) && (P.split || q_dtype != idx->store_dtype)) {
-      P.rescore = 1;
-      int64_t kf = static_cast<int64_t>(P.k_eff) + std::max<int64_t>(16, (P.k_eff + 3) / 4);
-      kf = (kf + 7) / 8 * 8;
-      P.k_fetch = static_cast<int>(std::max<int64_t>(P.k_eff, std::min<int64_t>(std::min<int64_t>(kf, NXF_MAX_K), idx->n)));
-    }
     P.n_tiles = ceil_div64(idx->n, 128);
     P.grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(idx->sm_count, P.n_tiles)));
     // overflow checks every `ce` tiles: short rows (few K blocks per tile) cannot afford a barrier per tile
-    P.rw = std::max(1, std::min(8, 16 / std::max<int>(1, static_cast<int>(idx->ld / 64) * (P.split ? 2 : 1))));
+    P.rw = std::max(1, std::min(8, 16 / std::max<int>(1, static_cast<int>(idx->ld / 64))));
     // epilogue warp sets: two while the filter keeps up, three / four once it is latency bound (search_stream_tc.cu); NXF_K2T_SETS=2..4 overrides
     {
       const int64_t nqp = round_up64(nq, 16);
@@ -633,16 +692,13 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     }
     P.cap = 2 * P.k_fetch + P.epi_sets * 128 * P.rw;   // pruned once more than 2k' entries are held (one round of appends on top)
     P.owners = static_cast<int64_t>(P.grid) * P.nq_t;
-    // threshold seeding (DESIGN.md "K2T"): one tile per CTA first, whole lists (<= 128 entries) into the arena, the sample's k'-th best
-    // into tau_g; pays off once every CTA streams many tiles (NXF_K2T_SEED=0/1 overrides)
-    // measured (C5, D = 64): the two extra launches cost ~0.1 ms and pay for themselves from nq * k' ~ 800 on (NXF_K2T_SEED=0/1 overrides)
+    // threshold seeding (DESIGN.md "K2T"): sample passes first, the sample's m-th best into tau_g.  With the estimate-only first pass
+    // the sample launches cost ~25 us: on 128-byte rows they pay from nq * k' ~ 200 on (C5 corpus, 16 queries k = 10: 0.309 -> 0.238 ms;
+    // one query k = 500: 0.280 -> 0.237 ms; one query k = 10: 0.218 -> 0.232 ms, left alone); long rows amortise the appends over more
+    // stream bytes and keep the old threshold (C2, 2-4 queries: -1 % with the launches).  NXF_K2T_SEED=0/1 overrides
     {
       const int seed_env = env_int("NXF_K2T_SEED", -1);
-      // with the estimate-only first pass the sample launches cost ~25 us: on 128-byte rows they pay from nq * k' ~ 200 on (C5 corpus,
-      // 16 queries k = 10: 0.309 -> 0.238 ms; one query k = 500: 0.280 -> 0.237 ms; one query k = 10: 0.218 -> 0.232 ms, left alone);
-      // long rows amortise the appends over more stream bytes and keep the old threshold (C2, 2-4 queries: -1 % with the launches)
-      const int64_t row_bytes_k2t = idx->ld * static_cast<int64_t>(dtype_size(idx->store_dtype));
-      const int64_t seed_from = row_bytes_k2t < 512 ? 192 : 768;
+      const int64_t seed_from = idx->ld * 2 < 512 ? 192 : 768;
       P.seed = seed_env >= 0 ? seed_env != 0 : (nq * static_cast<int64_t>(P.k_fetch) >= seed_from);
     }
     P.arena_stride = static_cast<int64_t>(P.grid) * P.k_fetch;
@@ -663,18 +719,6 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     if (cg != 1 && cg != 2) cg = (nq <= 128) ? 1 : 2;
     if (flags & NXF_SEARCH_TENSOR_1CTA) cg = 1;
     P.cta_group = cg;
-    // the MMA rounds the queries to the storage type: over-fetch and re-score in fp32 unless the
-    // caller's queries already are of that type (or asked not to)
-    const bool q_exact = !P.split && (q_dtype == idx->store_dtype);
-    if (!(flags & NXF_SEARCH_NO_RESCORE) && !q_exact) {
-      P.rescore = 1;
-      // over-fetch k' = k + max(16, k/4): the bf16 rounding of a unit query perturbs a score by ~6e-5 (1 sigma) while
-      // the gap between ranks k and 1.25k of a large corpus is tens of sigma (DESIGN.md "over-fetch")
-      int64_t kf = static_cast<int64_t>(P.k_eff) + std::max<int64_t>(16, (P.k_eff + 3) / 4);
-      kf = (kf + 7) / 8 * 8;
-      P.k_fetch = static_cast<int>(std::min<int64_t>(std::min<int64_t>(kf, NXF_MAX_K), idx->n));
-      P.k_fetch = std::max(P.k_fetch, P.k_eff);
-    }
     const int clusters = idx->sm_count / cg;
     // one launch serves at most one query tile per cluster (every cluster keeps <= 2 query tiles' state for the whole launch)
     P.batch = std::min<int64_t>(nq, static_cast<int64_t>(clusters) * 128 * cg);
@@ -689,7 +733,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       int a = used, b = P.num_qt;
       while (b) { const int t = a % b; a = b; b = t; }
       const int64_t unit_tiles = used / a;
-      const int64_t tile_bytes = 256 * row_bytes;
+      const int64_t tile_bytes = 256 * idx->ld * 2;
       const int64_t target = static_cast<int64_t>(std::max(1, env_int("NXF_K1_ROUND_MB", 32))) << 20;
       const int64_t m = std::max<int64_t>(1, (target + unit_tiles * tile_bytes / 2) / (unit_tiles * tile_bytes));
       P.round_tiles = static_cast<int>(std::min<int64_t>(unit_tiles * m, std::max<int64_t>(P.n_tiles, 1)));
@@ -707,7 +751,7 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     // overrides.  Measured (4 M rows, 16 384 queries, same box, one -> two sets): D = 64 +65 %, 128 +35 %, 256 +7 %, 320 +3 %, 384-512 +2 %,
     // 768 and 1536 +-0
     {
-      const int kb_tile = static_cast<int>(idx->ld / 64) * (P.split ? 3 : 1);
+      const int kb_tile = static_cast<int>(idx->ld / 64) * (P.seg_mode == 1 ? 3 : (P.seg_mode == 2 ? 2 : 1));
       // small searches (C1: 21 tile-units per cluster) lose 7 % to the second set's fixed costs (twice the lists to flush and merge)
       const int64_t units_per_cluster = static_cast<int64_t>(P.num_qt) * P.n_tiles / std::max(used, 1);
       P.epi_sets = std::max(1, std::min(2, env_int("NXF_K1_SETS", (kb_tile <= 8 && units_per_cluster >= 128) ? 2 : 1)));
@@ -720,27 +764,11 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
   return NXF_OK;
 }
 
-// out_packed != NULL (device pointer): the rows are written as 8-byte (score, shard-local row) entries instead of the two arrays
-static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, int k, float* out_scores,
-                       int64_t* out_ids, Entry* out_packed, int out_on_device, int flags, void* stream_) {
-  NXF_REQUIRE(idx != nullptr, "nxf_search: NULL index");
-  NXF_REQUIRE(nq >= 0, "nxf_search: negative query count");
-  NXF_REQUIRE(k >= 1 && k <= NXF_MAX_K, "nxf_search: k=%d outside [1, %d]", k, NXF_MAX_K);
-  if (nq == 0) return NXF_OK;
-  NXF_REQUIRE(q != nullptr && ((out_scores != nullptr && out_ids != nullptr) || out_packed != nullptr), "nxf_search: NULL buffer");
-  int rc = check_dtype(q_dtype, "nxf_search(q_dtype)");
-  if (rc) return rc;
-  if (q_ld == 0) q_ld = idx->dim;
-  NXF_REQUIRE(q_ld >= idx->dim, "nxf_search: query stride %lld smaller than dim %d", (long long)q_ld, idx->dim);
-  const int nforce = !!(flags & NXF_SEARCH_FORCE_EXACT) + !!(flags & NXF_SEARCH_FORCE_STREAM) + !!(flags & NXF_SEARCH_FORCE_TENSOR) +
-                     !!(flags & NXF_SEARCH_FORCE_TSTREAM);
-  NXF_REQUIRE(nforce <= 1, "nxf_search: more than one NXF_SEARCH_FORCE_* flag");
-
-  std::lock_guard<std::mutex> lk(idx->mu);
-  DeviceGuard g(idx->device);
-  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  UseScope use(idx, stream);
+// One level of the (certified) search over queries [0, nq).  Called with idx->mu held and the index's device current.
+// out_packed != NULL (device pointer): rows are written as 8-byte (score, shard-local row) entries instead of the two arrays.
+static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, int k, float* out_scores,
+                         int64_t* out_ids, Entry* out_packed, int out_on_device, int flags, cudaStream_t stream) {
+  int rc;
   const bool l2 = idx->metric == NXF_METRIC_L2;
   const int64_t total = nq * k;
 
@@ -754,15 +782,16 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
     // device outputs: run the arena merge over an all-empty arena (qcnt = 0)
   }
 
-  // fp32 storage: batches beyond the stream kernel's go to the tensor cores over the bf16 [hi | mid] shadow of the rows, built here
-  // on first use (NXF_F32_TENSOR=0 keeps them on the FFMA kernel)
-  bool split_ok = false;
-  if (idx->store_dtype == NXF_F32 && idx->n > 0 && !(flags & (NXF_SEARCH_FORCE_EXACT | NXF_SEARCH_FORCE_STREAM)) &&
-      ((flags & (NXF_SEARCH_FORCE_TENSOR | NXF_SEARCH_FORCE_TSTREAM)) ||
-       (nq >= env_int("NXF_TSTREAM_MIN_NQ_F32", 2) && env_int("NXF_F32_TENSOR", 1) != 0))) {
-    rc = ensure_split(idx, stream);
-    if (rc == NXF_OK) split_ok = true;
+  // fp32 storage goes to the tensor cores through its bf16 hi plane, built here on first use (NXF_F32_TENSOR=0 keeps it on the FFMA
+  // kernels); the mid plane is only built when the retry level needs it
+  bool hi_ok = false;
+  if (idx->store_dtype == NXF_F32 && idx->n > 0 && !(flags & (NXF_SEARCH_FORCE_EXACT | NXF_SEARCH_FORCE_STREAM | kFlagLevel3)) &&
+      ((flags & (NXF_SEARCH_FORCE_TENSOR | NXF_SEARCH_FORCE_TSTREAM | kFlagLevel2)) || env_int("NXF_F32_TENSOR", 1) != 0)) {
+    rc = ensure_plane(idx, 0, stream);
+    if (rc == NXF_OK && (flags & kFlagLevel2)) rc = ensure_plane(idx, 1, stream);
+    if (rc == NXF_OK) hi_ok = true;
     else if (rc != NXF_ENOMEM) return rc;
+    else if (flags & kFlagLevel2) flags = (flags & ~kFlagLevel2) | kFlagLevel3;   // no room for the mid plane: straight to the exact kernels
   }
 
   // plan; if the per-query arena forces several launches, re-plan for the launch size
@@ -770,7 +799,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
   int64_t batch = nq;
   for (int it = 0; it < 8; ++it) {
     P = SearchPlan();
-    rc = plan_search(idx, batch, q_dtype, k, flags, split_ok, &P);
+    rc = plan_search(idx, batch, q_dtype, k, flags, hi_ok, &P);
     if (rc) return rc;
     if (idx->n == 0) break;
     if (P.path == NXF_PATH_STREAM) { batch = std::min<int64_t>(nq, P.batch); break; }
@@ -783,7 +812,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
     if (batch <= max_q || it == 7) break;
     batch = max_q;
   }
-  if (idx->n == 0) { P.path = NXF_PATH_NONE; batch = nq; P.arena_stride = 1; P.owners = 0; P.cap = 1; P.k_fetch = 0; P.k_eff = 0; P.rescore = 0; }
+  if (idx->n == 0) { P.path = NXF_PATH_NONE; batch = nq; P.arena_stride = 1; P.owners = 0; P.cap = 1; P.k_fetch = 0; P.k_eff = 0; P.rescore = 0; P.cert = 0; }
   const bool multi_batch = batch < nq;
 
   // K1: the last launch of a multi-batch search holds fewer query tiles, so more clusters share a tile: its slices are longer
@@ -796,24 +825,32 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
     rem_arena = rem * rem_stride;
   }
 
+  // operands of the tensor paths: 16-bit rows as stored, or the bf16 planes of fp32 rows
+  const bool tpath = P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM;
+  const void* c_rows = P.use_hi ? idx->hi : idx->data;
+  const void* c_rows2 = P.seg_mode == 1 ? idx->mid : nullptr;
+  const int c_dt = P.use_hi ? NXF_BF16 : idx->store_dtype;
+  const int64_t q16_ld = P.seg_mode ? 2 * idx->ld : idx->ld;
+
   // ---- carve scratch (two passes: size, then pointers) ----
   const size_t qsz = dtype_size(q_dtype);
   unsigned char* base = nullptr;
   float* q_f32 = nullptr; void* q16 = nullptr; void* q_src = nullptr; uint32_t* tau_g = nullptr; uint32_t* qcnt = nullptr;
   Entry* arena = nullptr; Entry* cand = nullptr; float* o_scores = nullptr; int64_t* o_ids = nullptr; uint32_t* k2t_cnt = nullptr;
+  uint32_t* cert_w = nullptr;   // [nq] failure flags of the certificate, then one counter word
   const int64_t nq_pad = round_up64(batch, 256);
   for (int pass = 0; pass < 2; ++pass) {
     Carver cv(base);
     q_src = q_on_device ? nullptr : cv.take<unsigned char>(static_cast<size_t>(batch) * q_ld * qsz);
     q_f32 = cv.take<float>(static_cast<size_t>(nq_pad) * idx->ld);
-    q16 = (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * idx->ld * (P.split ? 2 : 1))
-                                                                    : nullptr;
+    q16 = tpath ? cv.take<uint16_t>(static_cast<size_t>(nq_pad) * q16_ld) : nullptr;
     // tau | qcnt | 64 control words: [0..5] K1 round counters (one per pass), [8] verification flag, [16..23] debug cycle counters
     tau_g = cv.take<uint32_t>(static_cast<size_t>(2 * nq_pad + 64));
     qcnt = tau_g ? tau_g + nq_pad : nullptr;
     arena = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(batch * P.arena_stride, rem_arena)));
     cand = cv.take<Entry>(static_cast<size_t>(std::max<int64_t>(P.owners, 1)) * P.cap);
     k2t_cnt = P.path == NXF_PATH_TSTREAM ? cv.take<uint32_t>(static_cast<size_t>(std::max<int64_t>(P.owners, 1))) : nullptr;
+    cert_w = P.cert ? cv.take<uint32_t>(static_cast<size_t>(nq) + 64) : nullptr;
     if (!out_on_device) {
       o_scores = cv.take<float>(static_cast<size_t>(batch) * k);
       o_ids = cv.take<int64_t>(static_cast<size_t>(batch) * k);
@@ -824,6 +861,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
       base = idx->scratch;
     }
   }
+  if (P.cert) NXF_CUDA(cudaMemsetAsync(cert_w + nq, 0, 64 * sizeof(uint32_t), stream));
 
   for (int64_t b0 = 0; b0 < nq; b0 += batch) {
     const int64_t bn = std::min(batch, nq - b0);
@@ -833,16 +871,16 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
       NXF_CUDA(cudaMemcpyAsync(q_src, qb, static_cast<size_t>(bn) * q_ld * qsz, cudaMemcpyHostToDevice, stream));
       q_dev = q_src;
     }
-    // queries -> fp32 [bn, ld] (zero padded); 16-bit copy for the MMA
+    // queries -> fp32 [bn, ld] (zero padded); 16-bit copy (or [hi | mid] planes) for the MMA
     rc = launch_convert_rows(q_dev, q_dtype, q_ld, q_f32, NXF_F32, idx->ld, bn, idx->dim, stream);
     if (rc) return rc;
     idx->stats.kernel_launches++;
-    if (P.split) {
-      rc = launch_split_rows(q_f32, idx->ld, q16, bn, stream);
+    if (tpath && P.seg_mode) {
+      rc = launch_split_rows(q_f32, idx->ld, q16, bn, c_dt, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
-    } else if (P.path == NXF_PATH_TENSOR || P.path == NXF_PATH_TSTREAM) {
-      rc = launch_convert_rows(q_dev, q_dtype, q_ld, q16, idx->store_dtype, idx->ld, bn, idx->dim, stream);
+    } else if (tpath) {
+      rc = launch_convert_rows(q_dev, q_dtype, q_ld, q16, c_dt, idx->ld, bn, idx->dim, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
     }
@@ -876,8 +914,6 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
     } else if (P.path == NXF_PATH_TSTREAM) {
       K2TParams kp;
       kp.n = idx->n; kp.nq = static_cast<int>(bn); kp.nq_pad = static_cast<int>(round_up64(bn, 16)); kp.kblocks = static_cast<int>(idx->ld / 64);
-      kp.split_kb = 0;
-      if (P.split) { kp.split_kb = kp.kblocks; kp.kblocks *= 2; }
       kp.stages = k2t_plan_stages(kp.kblocks, kp.nq_pad);
       kp.tbuf_stride = kp.nq_pad <= 32 ? 32 : (kp.nq_pad <= 64 ? 64 : 128);
       kp.tbufs = std::min(8, 512 / kp.tbuf_stride);
@@ -886,9 +922,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
       kp.epi_sets = P.epi_sets;
       kp.sink = sink;
       kp.sink.cap = P.cap;
-      const void* c_rows = P.split ? idx->split : idx->data;
-      const int64_t c_ld = P.split ? 2 * idx->ld : idx->ld;
-      const int c_dt = P.split ? NXF_BF16 : idx->store_dtype;
+      const int64_t c_ld = idx->ld;
       // Sampled thresholds, as in K1: up to two short launches over evenly spread sample tiles first (about one tile
       // per CTA, then about 16 more); after each, the seed kernel raises tau_g to the sample's m-th best over ALL lists of the
       // query (m from sample_rank(): at least k' rows of the corpus beat it except with probability ~e^-30).  The counts are
@@ -924,7 +958,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
         kp.tile_begin = (est_first && ps == 1) ? 0 : bounds[ps]; kp.tile_end = bounds[ps + 1];
         kp.first_pass = ps == 0 || (est_first && ps == 1); kp.last_pass = 0; kp.est_only = est ? 1 : 0;
         kp.no_check = (est || kp.tile_end - kp.tile_begin <= P.grid) ? 1 : 0;
-        rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
+        rc = launch_k2t(c_dt, q16, bn, q16_ld, c_rows, c_ld, kp, P.grid, stream);
         if (rc) return rc;
         kp.est_only = 0;
         const int m = std::min(P.k_fetch, sample_rank(P.k_fetch, bounds[ps + 1], P.n_tiles));
@@ -940,7 +974,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
       kp.tile_begin = bounds[n_pass - 1]; kp.tile_end = P.n_tiles;
       kp.first_pass = n_pass == 1; kp.last_pass = 1; kp.no_check = 0;
       if (n_pass > 1) {
-        rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
+        rc = launch_k2t(c_dt, q16, bn, q16_ld, c_rows, c_ld, kp, P.grid, stream);
         if (rc) return rc;
         uint32_t* flag = tau_g + 2 * nq_pad + 8;
         rc = launch_verify_counts(qcnt, tau_g, bn, static_cast<int>(std::min<int64_t>(P.k_fetch, idx->n)), flag, stream);
@@ -949,7 +983,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
         // the fall-back launch: everything again from empty lists, for the queries the verification reset (all others: tau = +inf)
         kp.tile_begin = 0; kp.first_pass = 1; kp.run_flag = flag;
       }
-      rc = launch_k2t(c_dt, q16, bn, c_rows, c_ld, kp, P.grid, stream);
+      rc = launch_k2t(c_dt, q16, bn, q16_ld, c_rows, c_ld, kp, P.grid, stream);
       if (rc) return rc;
       idx->stats.kernel_launches++;
     } else if (P.path == NXF_PATH_EXACT) {
@@ -964,8 +998,8 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
     } else if (P.path == NXF_PATH_TENSOR) {
       K1Params kp;
       kp.n = idx->n; kp.nq = bn; kp.kblocks = static_cast<int>(idx->ld / 64);
-      kp.split_kb = 0;
-      if (P.split) { kp.split_kb = kp.kblocks; kp.kblocks *= 3; }
+      kp.split_kb = 0; kp.seg_mode = P.seg_mode;
+      if (P.seg_mode) { kp.split_kb = kp.kblocks; kp.kblocks *= (P.seg_mode == 1 ? 3 : 2); }
       kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group));
       kp.epi_sets = P.epi_sets;
       kp.half_norm = l2 ? idx->half_norm : nullptr;
@@ -1016,8 +1050,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
         kp.sink.k = passes[ps].k;
         kp.debug = user_debug | (passes[ps].est_only ? 128 : 0);
         kp.sync_ctr = tau_g + 2 * nq_pad + ps;   // one round counter per pass (all zeroed above)
-        rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
-                     : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
+        rc = launch_k1(c_dt, P.cta_group, q16, bn, q16_ld, c_rows, c_rows2, idx->ld, kp, grid, stream);
         if (rc) return rc;
         idx->stats.kernel_launches++;
         if (ps + 1 < n_pass) {
@@ -1035,8 +1068,7 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
         kp.tile_begin = 0; kp.tile_end = P.n_tiles; kp.sink.k = P.k_fetch;
         kp.run_flag = flag;
         kp.sync_ctr = tau_g + 2 * nq_pad + 5;
-        rc = P.split ? launch_k1(NXF_BF16, P.cta_group, q16, bn, idx->split, 2 * idx->ld, kp, grid, stream)
-                     : launch_k1(idx->store_dtype, P.cta_group, q16, bn, idx->data, idx->ld, kp, grid, stream);
+        rc = launch_k1(c_dt, P.cta_group, q16, bn, q16_ld, c_rows, c_rows2, idx->ld, kp, grid, stream);
         if (rc) return rc;
         idx->stats.kernel_launches += 2;
       }
@@ -1057,6 +1089,8 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
     mp.arena = arena; mp.qcnt = qcnt; mp.arena_stride = arena_stride; mp.k_fetch = P.k_fetch; mp.k_out = k; mp.metric = idx->metric;
     mp.rescore = P.rescore; mp.q = q_f32; mp.ldq = idx->ld; mp.corpus = idx->data; mp.ld = idx->ld; mp.dim = idx->dim;
     mp.id_offset = idx->id_offset;
+    mp.cert = P.cert; mp.eps_rel = P.eps_rel; mp.eps_abs = P.eps_abs; mp.max_norm2 = idx->max_norm2; mp.n_rows = idx->n;
+    mp.cert_fail = P.cert ? cert_w + b0 : nullptr; mp.cert_count = P.cert ? cert_w + nq : nullptr;
     mp.out_scores = out_on_device ? (out_scores ? out_scores + b0 * k : nullptr) : o_scores;
     mp.out_ids = out_on_device ? (out_ids ? out_ids + b0 * k : nullptr) : o_ids;
     mp.out_packed = out_packed ? out_packed + b0 * k : nullptr;
@@ -1075,7 +1109,111 @@ static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
   idx->stats.last_k_fetch = P.k_fetch;
   idx->stats.last_chunks = P.chunks;
   idx->stats.last_grid = P.grid;
+  if (!P.cert) return NXF_OK;
+
+  // ---- certificate: how many queries could not be certified?  (4 bytes back; the stream is drained here, which is what makes a
+  // certified device-in / device-out search synchronous on its stream) ----
+  uint32_t n_fail = 0;
+  NXF_CUDA(cudaMemcpyAsync(&n_fail, cert_w + nq, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+  NXF_CUDA(cudaStreamSynchronize(stream));
+  idx->stats.cert_checked += nq;
+  if (n_fail == 0) return NXF_OK;
+
+  // ---- widen and retry: the failed queries go through the next level (segmented K1, then the exact fp32 kernels) ----
+  std::vector<uint32_t> h_fail(static_cast<size_t>(nq));
+  NXF_CUDA(cudaMemcpy(h_fail.data(), cert_w, static_cast<size_t>(nq) * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  std::vector<int64_t> rows;
+  rows.reserve(n_fail);
+  for (int64_t i = 0; i < nq; ++i) if (h_fail[static_cast<size_t>(i)]) rows.push_back(i);
+  const int64_t nf = static_cast<int64_t>(rows.size());
+  if (nf == 0) return NXF_OK;
+  const int next_level = P.level == 1 ? 2 : 3;
+  if (next_level == 2) idx->stats.cert_retry_l2 += nf; else idx->stats.cert_retry_l3 += nf;
+  const int next_flags = (flags & ~(kForceMask | kFlagLevel2 | kFlagLevel3 | NXF_SEARCH_TENSOR_1CTA)) | (next_level == 2 ? kFlagLevel2 : kFlagLevel3);
+  const nxf_stats keep_stats = idx->stats;
+  const size_t row_bytes_q = static_cast<size_t>(q_ld) * qsz;
+  if (!q_on_device && !out_on_device) {
+    // host in, host out: compact on the host
+    std::vector<unsigned char> hq(static_cast<size_t>(nf) * row_bytes_q);
+    for (int64_t i = 0; i < nf; ++i) std::memcpy(hq.data() + static_cast<size_t>(i) * row_bytes_q, static_cast<const unsigned char*>(q) + static_cast<size_t>(rows[i]) * row_bytes_q, row_bytes_q);
+    std::vector<float> hs(static_cast<size_t>(nf) * k);
+    std::vector<int64_t> hi(static_cast<size_t>(nf) * k);
+    rc = search_locked(idx, hq.data(), nf, q_dtype, q_ld, 0, k, hs.data(), hi.data(), nullptr, 0, next_flags, stream);
+    if (rc) return rc;
+    for (int64_t i = 0; i < nf; ++i) {
+      std::memcpy(out_scores + rows[i] * k, hs.data() + i * k, static_cast<size_t>(k) * sizeof(float));
+      std::memcpy(out_ids + rows[i] * k, hi.data() + i * k, static_cast<size_t>(k) * sizeof(int64_t));
+    }
+  } else {
+    // any device side: compacted queries and the retry's results live in temporary device buffers (a rare path: plain cudaMalloc)
+    unsigned char* d_q = nullptr; int64_t* d_rows = nullptr; float* d_s = nullptr; int64_t* d_i = nullptr; Entry* d_p = nullptr;
+    auto cleanup = [&]() { cudaFree(d_q); cudaFree(d_rows); cudaFree(d_s); cudaFree(d_i); cudaFree(d_p); };
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&d_q), static_cast<size_t>(nf) * row_bytes_q);
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&d_rows), static_cast<size_t>(nf) * sizeof(int64_t));
+    if (e == cudaSuccess && out_packed) e = cudaMalloc(reinterpret_cast<void**>(&d_p), static_cast<size_t>(nf) * k * sizeof(Entry));
+    if (e == cudaSuccess && !out_packed) e = cudaMalloc(reinterpret_cast<void**>(&d_s), static_cast<size_t>(nf) * k * sizeof(float));
+    if (e == cudaSuccess && !out_packed) e = cudaMalloc(reinterpret_cast<void**>(&d_i), static_cast<size_t>(nf) * k * sizeof(int64_t));
+    if (e != cudaSuccess) { cleanup(); return cuda_fail(e, "cudaMalloc(retry buffers)", __FILE__, __LINE__); }
+    e = cudaMemcpyAsync(d_rows, rows.data(), static_cast<size_t>(nf) * sizeof(int64_t), cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) { cleanup(); return cuda_fail(e, "cudaMemcpyAsync(retry rows)", __FILE__, __LINE__); }
+    if (q_on_device) {
+      rc = launch_gather_rows(q, static_cast<int64_t>(row_bytes_q), d_rows, nf, d_q, stream);
+    } else {
+      std::vector<unsigned char> hq(static_cast<size_t>(nf) * row_bytes_q);
+      for (int64_t i = 0; i < nf; ++i) std::memcpy(hq.data() + static_cast<size_t>(i) * row_bytes_q, static_cast<const unsigned char*>(q) + static_cast<size_t>(rows[i]) * row_bytes_q, row_bytes_q);
+      e = cudaMemcpy(d_q, hq.data(), hq.size(), cudaMemcpyHostToDevice);
+      rc = e == cudaSuccess ? NXF_OK : cuda_fail(e, "cudaMemcpy(retry queries)", __FILE__, __LINE__);
+    }
+    if (rc == NXF_OK) rc = search_locked(idx, d_q, nf, q_dtype, q_ld, 1, k, d_s, d_i, d_p, 1, next_flags, stream);
+    if (rc == NXF_OK) {
+      if (out_on_device) {
+        rc = launch_scatter_results(d_s, d_i, d_p, d_rows, nf, k, out_scores, out_ids, out_packed, stream);
+      } else {
+        std::vector<float> hs(static_cast<size_t>(nf) * k);
+        std::vector<int64_t> hi(static_cast<size_t>(nf) * k);
+        e = cudaMemcpyAsync(hs.data(), d_s, hs.size() * sizeof(float), cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(hi.data(), d_i, hi.size() * sizeof(int64_t), cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "retry results", __FILE__, __LINE__);
+        else for (int64_t i = 0; i < nf; ++i) {
+          std::memcpy(out_scores + rows[i] * k, hs.data() + i * k, static_cast<size_t>(k) * sizeof(float));
+          std::memcpy(out_ids + rows[i] * k, hi.data() + i * k, static_cast<size_t>(k) * sizeof(int64_t));
+        }
+      }
+    }
+    cudaStreamSynchronize(stream);
+    cleanup();
+    if (rc) return rc;
+  }
+  // the primary level describes the search in the stats; the retry only adds its counters
+  idx->stats.last_path = keep_stats.last_path; idx->stats.last_k_fetch = keep_stats.last_k_fetch;
+  idx->stats.last_chunks = keep_stats.last_chunks; idx->stats.last_grid = keep_stats.last_grid;
+  idx->stats.searches = keep_stats.searches;
   return NXF_OK;
+}
+
+static int search_impl(nxf_index* idx, const void* q, int64_t nq, int q_dtype, int64_t q_ld, int q_on_device, int k, float* out_scores,
+                       int64_t* out_ids, Entry* out_packed, int out_on_device, int flags, void* stream_) {
+  NXF_REQUIRE(idx != nullptr, "nxf_search: NULL index");
+  NXF_REQUIRE(nq >= 0, "nxf_search: negative query count");
+  NXF_REQUIRE(k >= 1 && k <= NXF_MAX_K, "nxf_search: k=%d outside [1, %d]", k, NXF_MAX_K);
+  if (nq == 0) return NXF_OK;
+  NXF_REQUIRE(q != nullptr && ((out_scores != nullptr && out_ids != nullptr) || out_packed != nullptr), "nxf_search: NULL buffer");
+  int rc = check_dtype(q_dtype, "nxf_search(q_dtype)");
+  if (rc) return rc;
+  if (q_ld == 0) q_ld = idx->dim;
+  NXF_REQUIRE(q_ld >= idx->dim, "nxf_search: query stride %lld smaller than dim %d", (long long)q_ld, idx->dim);
+  NXF_REQUIRE((flags & ~(kForceMask | NXF_SEARCH_NO_RESCORE | NXF_SEARCH_TENSOR_1CTA)) == 0, "nxf_search: unknown flag bits 0x%x", flags);
+  const int nforce = !!(flags & NXF_SEARCH_FORCE_EXACT) + !!(flags & NXF_SEARCH_FORCE_STREAM) + !!(flags & NXF_SEARCH_FORCE_TENSOR) +
+                     !!(flags & NXF_SEARCH_FORCE_TSTREAM);
+  NXF_REQUIRE(nforce <= 1, "nxf_search: more than one NXF_SEARCH_FORCE_* flag");
+
+  std::lock_guard<std::mutex> lk(idx->mu);
+  DeviceGuard g(idx->device);
+  if (!g.ok) return cuda_fail(cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  UseScope use(idx, stream);
+  return search_locked(idx, q, nq, q_dtype, q_ld, q_on_device, k, out_scores, out_ids, out_packed, out_on_device, flags, stream);
 }
 
 extern "C" {

@@ -47,27 +47,31 @@ int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* ds
   return NXF_EINVAL;
 }
 
-// fp32 rows -> two bf16 planes per row, [hi(ld) | mid(ld)]: hi = bf16(x), mid = bf16(x - hi).  x = hi + mid up to 2^-17 |x|, so the three
-// bf16 products q_hi*c_hi + q_hi*c_mid + q_mid*c_hi reproduce an fp32 inner product to ~2^-16 per term -- the operand layout of the
-// tensor-core path over fp32 storage (DESIGN.md "fp32 on tcgen05").
-__global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict__ src, int64_t ld, __nv_bfloat16* __restrict__ dst, int64_t n) {
+// fp32 rows -> two 16-bit planes per row, [hi(ld) | mid(ld)]: hi = T(x), mid = T(x - hi), so x = hi + mid up to 2^-17 |x| (bf16; less for
+// f16).  The QUERY operand of the segmented retry level of the certified search (K1Params::seg_mode): with the corpus planes of
+// fp32 storage the three products q_hi*c_hi + q_hi*c_mid + q_mid*c_hi reproduce an fp32 inner product to ~2^-16 per term; with
+// 16-bit storage q_hi*c + q_mid*c removes the query rounding.
+template <typename T>
+__global__ void __launch_bounds__(256) split_rows_kernel(const float* __restrict__ src, int64_t ld, T* __restrict__ dst, int64_t n) {
   const int64_t total = n * ld;
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int64_t r = i / ld;
     const int64_t d = i - r * ld;
     const float x = src[i];
-    const __nv_bfloat16 hi = __float2bfloat16_rn(x);
-    const __nv_bfloat16 mid = __float2bfloat16_rn(x - __bfloat162float(hi));
+    const T hi = from_f32<T>(x);
+    const T mid = from_f32<T>(x - to_f32<T>(hi));
     dst[r * 2 * ld + d] = hi;
     dst[r * 2 * ld + ld + d] = mid;
   }
 }
 
-int launch_split_rows(const float* src, int64_t ld, void* dst, int64_t n, cudaStream_t stream) {
+int launch_split_rows(const float* src, int64_t ld, void* dst, int64_t n, int dst_dtype, cudaStream_t stream) {
   if (n <= 0) return NXF_OK;
   const int grid = static_cast<int>(std::min<int64_t>(ceil_div64(n * ld, 256), 148 * 16));
-  split_rows_kernel<<<grid, 256, 0, stream>>>(src, ld, static_cast<__nv_bfloat16*>(dst), n);
+  if (dst_dtype == NXF_BF16) split_rows_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(src, ld, static_cast<__nv_bfloat16*>(dst), n);
+  else if (dst_dtype == NXF_F16) split_rows_kernel<__half><<<grid, 256, 0, stream>>>(src, ld, static_cast<__half*>(dst), n);
+  else { set_error("split_rows: bad plane dtype %d", dst_dtype); return NXF_EINVAL; }
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
 }

@@ -203,7 +203,7 @@ int launch_subset_search(int store_dtype, const SubsetParams& p, int64_t nq, cud
 int launch_positive_rank(const float* pos, const float* topk, int64_t nq, int k, int32_t* rank, uint8_t* pred, cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,
                         cudaStream_t stream);
-int launch_split_rows(const float* src, int64_t ld, void* dst, int64_t n, cudaStream_t stream);
+int launch_split_rows(const float* src, int64_t ld, void* dst, int64_t n, int dst_dtype, cudaStream_t stream);
 int launch_mid_rows(const float* src, int64_t ld, void* dst, int64_t n, cudaStream_t stream);
 int launch_row_norm_max(const void* rows, int dtype, int64_t ld, int64_t n, int dim, uint32_t* max_norm2, cudaStream_t stream);
 int launch_gather_rows(const void* src, int64_t row_bytes, const int64_t* rows, int64_t n, void* dst, cudaStream_t stream);

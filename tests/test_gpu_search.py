@@ -82,14 +82,10 @@ def test_exact_kernel(case, store):
 def test_stream_kernel(case, nq, store):
     n, d, k = case
     c, x = gen_inputs(n, d, nq, seed=200 + d)
-    # 16-bit storage with more than one query goes to the tensor-core streaming kernel (K2T); K2 keeps nq = 1 and fp32 storage
-    # ... and single queries on long rows (>= 512 B), where it already sits on the HBM roofline
-    # fp32 storage: K2 for one query, K2T over the bf16 [hi | mid] shadow from two
-    long_rows = (d + 63) // 64 * 64 * 2 >= 512
-    k2 = nq == 1 and (store == "f32" or long_rows)
-    run_and_check(c, x, k, store=store, path="auto", expect_path="stream" if k2 else "tstream")
-    if not k2:
-        run_and_check(c, x, k, store=store, path="stream", expect_path="stream")
+    # round 2: every small batch that fits goes to the tensor-core streaming kernel (K2T) -- one query and fp32 storage (through its
+    # bf16 hi plane, certified) included; K2 (CUDA cores, exact fp32 FMAs) stays reachable by flag and serves the exact retry level
+    run_and_check(c, x, k, store=store, path="auto", expect_path="tstream")
+    run_and_check(c, x, k, store=store, path="stream", expect_path="stream")
 
 
 @pytest.mark.parametrize("store", ["bf16", "f16"])
@@ -108,12 +104,12 @@ def test_tensor_stream_kernel(case, store):
 
 @pytest.mark.parametrize("case", [
     # N, D, Q, k, expected default path
-    (3000, 64, 1, 10, "stream"), (3000, 64, 2, 10, "tstream"), (3000, 64, 16, 10, "tstream"), (5000, 128, 17, 100, "tstream"), (20000, 384, 33, 10, "tstream"),
-    (9000, 768, 32, 100, "tstream"), (9000, 768, 64, 100, "tensor"), (4096, 96, 100, 500, "tstream"), (2500, 100, 5, 7, "tstream"),
+    (3000, 64, 1, 10, "tstream"), (3000, 64, 2, 10, "tstream"), (3000, 64, 16, 10, "tstream"), (5000, 128, 17, 100, "tstream"), (20000, 384, 33, 10, "tstream"),
+    (9000, 768, 32, 100, "tstream"), (9000, 768, 64, 100, "tstream"), (9000, 768, 128, 100, "tensor"), (4096, 96, 100, 500, "tstream"), (2500, 100, 5, 7, "tstream"),
     (40000, 64, 128, 500, "tstream"), (7001, 1536, 16, 10, "tstream"),
 ])
 def test_tensor_stream_kernel_fp32_storage(case):
-    """K2T over the bf16 [hi | mid] shadow of fp32 rows: a c_hi block meets q_hi and q_mid, a c_mid block q_hi."""
+    """K2T over the bf16 hi plane of fp32 rows (2 bytes per element streamed), fp32 re-score, certificate."""
     n, d, q, k, expect = case
     c, x = gen_inputs(n, d, q, seed=700 + n % 67)
     run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, expect_path=expect)
@@ -178,18 +174,18 @@ def test_tensor_kernel_rescored(case, store):
 
 @pytest.mark.parametrize("case", CASES + [(60000, 384, 700, 100), (30000, 1024, 300, 10)])
 def test_tensor_kernel_fp32_storage(case):
-    """fp32 rows on tcgen05: the rows' bf16 [hi | mid] shadow, three MMA segments per tile (q_hi c_hi + q_hi c_mid + q_mid c_hi),
-    over-fetch and fp32 re-score.  Default dispatch above the stream kernel's batch; results to the fp32 tolerance."""
+    """fp32 rows on tcgen05 (certified search): the candidate pass streams the rows' bf16 hi plane, k' = 4k candidates are re-scored
+    in fp32 and certified.  Default dispatch above the stream kernels' batch; results to the fp32 tolerance."""
     n, d, q, k = case
     c, x = gen_inputs(n, d, q, seed=600 + n % 71)
     run_and_check(c, x, k, store="f32", path="auto", rtol=1e-5, expect_path="tensor" if q > 128 else "tstream")
     run_and_check(c, x, k, store="f32", path="tensor", rtol=1e-5, expect_path="tensor")
-    # without the re-score the scores are the three-product sums themselves: 2^-16 per term
-    run_and_check(c, x, k, store="f32", path="tensor_raw", rtol=2e-5, atol=4e-6, expect_path="tensor", min_recall=0.999)
+    # without the re-score the scores are the candidate pass itself: bf16(q) . bf16(c)
+    run_and_check(c, x, k, store="f32", path="tensor_raw", rtol=2e-4, atol=2e-5, expect_path="tensor", min_recall=0.999)
 
 
 def test_tensor_fp32_storage_follows_adds_and_reset():
-    """The shadow is built on first use and extended / rebuilt when rows are added, the storage grows or the index is reset."""
+    """The bf16 plane is built on first use and extended / rebuilt when rows are added, the storage grows or the index is reset."""
     from nexus_b200 import FlatIndex
     c, x = gen_inputs(9000, 200, 200, seed=31)
     idx = FlatIndex(200, "ip", "f32")
