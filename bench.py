@@ -418,7 +418,6 @@ def small_batch_records(torch, idx, q, k, N, D, store, peaks, nqs=(1, 32, 128), 
     """The memory-bound path on the resident corpus, the way the reference CALLS search (serve nq = 1, eval chunk 32, recsys 128):
     kernel time from the library's CUDA events, achieved GB/s = N*ld*sizeof(T) / kernel time."""
     out = []
-    esz = 4 if store == "f32" else 2
     ld = (D + 63) // 64 * 64
     for nq in nqs:
         qq = q[:nq].contiguous()
@@ -436,9 +435,11 @@ def small_batch_records(torch, idx, q, k, N, D, store, peaks, nqs=(1, 32, 128), 
         idx.set_profiling(False)
         kms = st["main_kernel_ms"] / max(1, st["main_kernel_count"])
         call = e0.elapsed_time(e1) / iters
+        # bytes the kernel streams per corpus element: the tensor paths read 16-bit rows (fp32 storage: its bf16 plane), K2 / KX the rows as stored
+        esz = 2 if (store != "f32" or st["last_path_name"] in ("tstream", "tensor")) else 4
         gbs = N * ld * esz / (kms * 1e-3) / 1e9
-        out.append({"nq": nq, "k": k, "path": st["last_path_name"], "kernel_ms": kms, "call_ms": call, "GBps": gbs,
-                    "frac": gbs / peaks["hbm_gbs"], "queries_per_s": nq / (call * 1e-3)})
+        out.append({"nq": nq, "k": k, "path": st["last_path_name"], "kernel_ms": kms, "call_ms": call, "host_and_merge_ms": call - kms,
+                    "streamed_bytes_per_element": esz, "GBps": gbs, "frac": gbs / peaks["hbm_gbs"], "queries_per_s": nq / (call * 1e-3)})
     return out
 
 

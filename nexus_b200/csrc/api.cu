@@ -233,8 +233,6 @@ void plan_units(int num_qt, int64_t n_tiles, int grid, int* chunks_out, int64_t*
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// K1's arena slice of a query: the list left by the sample passes (<= k' entries) + up to k' entries from every cluster that owns a
-// piece of the query's tile in the last pass (a tile's line segment is cut by pieces of num_qt / clusters of its length)
 // Host rows -> pinned staging with several threads: one thread copies at 8-12 GB/s, a Gen5 x16 link moves ~55 GB/s, so the
 // add of a host corpus (utils.py:169,189: N*D*4 bytes) is bound by this copy unless it is split (NXF_ADD_THREADS, default 8).
 void parallel_memcpy(unsigned char* dst, const unsigned char* src, size_t bytes, int threads) {
@@ -250,9 +248,13 @@ void parallel_memcpy(unsigned char* dst, const unsigned char* src, size_t bytes,
   for (auto& x : th) x.join();
 }
 
-int64_t k1_arena_stride(int64_t clusters, int64_t num_qt, int k_fetch, int epi_sets) {
+// K1's arena slice of a query (a tile's line segment is cut by pieces of num_qt / clusters of its length: owners_max clusters own
+// a piece of one query tile)
+int64_t k1_arena_stride(int64_t clusters, int64_t num_qt, int k_fetch, int epi_sets, int cap) {
   const int64_t owners_max = std::min<int64_t>(clusters, (clusters + num_qt - 1) / std::max<int64_t>(num_qt, 1) + 1);
-  return (owners_max * epi_sets + 1) * k_fetch;  // every epilogue set of an owning cluster flushes its own list
+  // every epilogue set of an owning cluster flushes whatever its row holds at the end of a pass (<= cap entries, no prune first),
+  // on top of the list the earlier passes left (<= k')
+  return owners_max * epi_sets * cap + k_fetch;
 }
 
 // Rank m in a sample of `s_tiles` of `n_tiles` corpus tiles whose score is, except with probability < e^-30 per query, exceeded by
@@ -757,9 +759,9 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       P.epi_sets = std::max(1, std::min(2, env_int("NXF_K1_SETS", (kb_tile <= 8 && units_per_cluster >= 128) ? 2 : 1)));
     }
     P.owners = static_cast<int64_t>(P.grid) * 128 * 2 * P.epi_sets;  // two query-tile slots per CTA, one buffer per (slot, set, row)
-    // arena slice of a query: the list left by the sample passes (<= k' entries) + up to k' entries from every cluster that owns
-    // a piece of the query tile in the last pass
-    P.arena_stride = k1_arena_stride(used, P.num_qt, P.k_fetch, P.epi_sets);
+    // arena slice of a query: the list left by the sample passes (<= k' entries) + up to cap entries from every (cluster, set) that
+    // owns a piece of the query tile in a pass
+    P.arena_stride = k1_arena_stride(used, P.num_qt, P.k_fetch, P.epi_sets, P.cap);
   }
   return NXF_OK;
 }
@@ -821,7 +823,7 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
     const int64_t rem = nq % batch;
     const int64_t nqt = ceil_div64(rem, 128 * P.cta_group);
     const int64_t cl = std::max<int64_t>(1, std::min<int64_t>(P.grid / P.cta_group, nqt * P.n_tiles));
-    rem_stride = k1_arena_stride(cl, nqt, P.k_fetch, P.epi_sets);
+    rem_stride = k1_arena_stride(cl, nqt, P.k_fetch, P.epi_sets, P.cap);
     rem_arena = rem * rem_stride;
   }
 

@@ -430,16 +430,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       Entry* warp_buf0 = slot_buf0(slot);
       const int64_t my_q = slot_qrow0(slot) + lane;
       if (my_q >= p.nq) my_cnt = 0;
-      // rows holding more than sink.k entries are reduced first (rare once the thresholds are sampled)
-      unsigned big = __ballot_sync(kFullMask, my_cnt > k);
-      while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const int n_src = __shfl_sync(kFullMask, my_cnt, src);
-        warp_prune(warp_buf0 + static_cast<int64_t>(src) * cap, n_src, k);
-        if (static_cast<int>(lane) == src) my_cnt = k;
-        __syncwarp();
-      }
+      // Everything a row holds goes out (<= cap entries; the slice is sized for it, api.cu k1_arena_stride).  Round 1 reduced rows
+      // holding more than sink.k entries to their k best first -- a serial warp-cooperative select per row, up to 64 of them per
+      // warp: ~0.13 ms at the end of EVERY pass, sample passes included (their rows all hold more than the sample rank m), which
+      // was most of what a 1/8 shard paid on top of its GEMM.  select_tau_kernel / merge_arena_kernel select over the union anyway.
       // one atomic per row, all 32 in flight together; then the warp copies the rows one after the other
       uint32_t my_pos = 0;
       if (my_cnt > 0) my_pos = atomicAdd(&p.sink.qcnt[my_q], static_cast<uint32_t>(my_cnt));

@@ -282,7 +282,7 @@ def test_tensor_default_dispatch_and_bf16_recall_vs_fp32():
     c, x = gen_inputs(50000, 768, 512, seed=77)
     c = oracle.round_to_bf16(c)                     # the corpus IS bf16 (config 2's wording)
     idx, D, I, rep, st = run_and_check(c, x, 100, store="bf16", path="auto", expect_path="tensor", min_recall=0.999)
-    assert st["last_k_fetch"] == 128
+    assert st["last_k_fetch"] == 200 and st["cert_checked"] == 512 and st["cert_retry_l2"] == 0      # k' = 2k, every query certified
 
 
 def test_multiple_adds_and_reset():
