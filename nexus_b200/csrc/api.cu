@@ -701,7 +701,10 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
     {
       const int seed_env = env_int("NXF_K2T_SEED", -1);
       const int64_t seed_from = idx->ld * 2 < 512 ? 192 : 768;
-      P.seed = seed_env >= 0 ? seed_env != 0 : (nq * static_cast<int64_t>(P.k_fetch) >= seed_from);
+      // round 2: also whenever the unseeded search would leave one list of k' per CTA for the arena merge to reduce (grid * k' entries
+      // per query: one query, k' = 200 on C2 = 29 600 entries, 0.16-0.27 ms in a single merge CTA -- more than the sample launches cost)
+      const bool big_arena = static_cast<int64_t>(P.grid) * P.k_fetch >= env_int("NXF_K2T_SEED_ARENA", 4096);
+      P.seed = seed_env >= 0 ? seed_env != 0 : (nq * static_cast<int64_t>(P.k_fetch) >= seed_from || big_arena);
     }
     P.arena_stride = static_cast<int64_t>(P.grid) * P.k_fetch;
     P.batch = std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ);

@@ -8,6 +8,8 @@
 //   merge_lists_kernel : one CTA per query.  Input: n_lists sorted per-shard lists (the result of the
 //       NCCL all-gather in the row-sharded multi-GPU search, replacing Faiss IndexShards' host merge
 //       behind utils.py:178-183).  Same select + sort on (score, global id).
+#include <cstdlib>
+
 #include "params.cuh"
 #include "block_sort.cuh"
 
@@ -476,8 +478,94 @@ __global__ void __launch_bounds__(mg::THREADS) merge_lists_kernel(const __grid_c
   }
 }
 
+// The same merge for lists that ARE sorted best-first (every list nxf_search / nxf_search_packed writes is: score descending, id
+// ascending among equal scores), without selection or sorting: an entry's place in the merged order is its position in its own list
+// plus, for every other list, the number of entries that precede it there -- a binary search.  One CTA per query, the 64-bit keys
+// (monotone score key | inverted id) of all lists in shared memory, one barrier.  2 lists x 100: 0.14 ms -> ~20 us for 6 980 queries.
+constexpr int kRankMergeMax = 4096;   // entries per query (n_lists * k) served by this kernel; beyond: the select + sort kernel
+template <bool PACKED>
+__global__ void __launch_bounds__(128) merge_sorted_lists_kernel(const __grid_constant__ MergeListsParams p) {
+  extern __shared__ __align__(16) unsigned char ms_smem[];
+  const int M = p.n_lists * p.k;
+  uint64_t* keys = reinterpret_cast<uint64_t*>(ms_smem);            // [M]
+  int64_t* pay = reinterpret_cast<int64_t*>(ms_smem + static_cast<size_t>(M) * 8);  // [M]
+  __shared__ int sh_valid;
+  const int64_t qi = blockIdx.x;
+  const int tid = threadIdx.x;
+  const bool l2 = p.metric == NXF_METRIC_L2;
+  if (tid == 0) sh_valid = 0;
+  __syncthreads();
+  int valid = 0;
+  for (int i = tid; i < M; i += 128) {
+    const int l = i / p.k, j = i - l * p.k;
+    const int64_t at = (static_cast<int64_t>(l) * p.nq + qi) * p.k + j;
+    float sc;
+    int64_t id;
+    if (PACKED) {
+      const Entry e = p.packed[at];
+      sc = e.score;
+      id = e.row < 0 ? -1 : static_cast<int64_t>(e.row) + p.offs[l];
+    } else {
+      sc = p.scores[at];
+      id = p.ids[at];
+    }
+    uint64_t kk = 0;   // padding: below every real key
+    if (id >= 0) {
+      const uint32_t low = static_cast<uint32_t>(0x7FFFFFFF) - static_cast<uint32_t>(id > 0x7FFFFFFE ? 0x7FFFFFFE : id);
+      kk = (static_cast<uint64_t>(okey(l2 ? -sc : sc)) << 32) | low;
+      ++valid;
+    }
+    keys[i] = kk;
+    pay[i] = id;
+  }
+  if (valid) atomicAdd(&sh_valid, valid);
+  __syncthreads();
+  const int total = sh_valid;
+  for (int i = tid; i < M; i += 128) {
+    const uint64_t kk = keys[i];
+    if (kk == 0) continue;
+    const int l = i / p.k, j = i - l * p.k;
+    int rank = j;                                   // the entries before it in its own (sorted) list
+    for (int o = 0; o < p.n_lists && rank < p.k_out; ++o) {
+      if (o == l) continue;
+      const uint64_t* lst = keys + o * p.k;
+      // number of entries of list o that come first: key greater, or equal and the list has the smaller index
+      int lo = 0, hi = p.k;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const uint64_t km = lst[mid];
+        if (km > kk || (km == kk && o < l)) lo = mid + 1; else hi = mid;
+      }
+      rank += lo;
+    }
+    if (rank < p.k_out) {
+      const float sc = okey_inv(static_cast<uint32_t>(kk >> 32));
+      p.out_scores[qi * p.k_out + rank] = l2 ? -sc : sc;
+      p.out_ids[qi * p.k_out + rank] = pay[i];
+    }
+  }
+  for (int j = total + tid; j < p.k_out; j += 128) {
+    p.out_scores[qi * p.k_out + j] = l2 ? FLT_MAX : -FLT_MAX;
+    p.out_ids[qi * p.k_out + j] = -1;
+  }
+}
+
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream) {
   if (p.nq <= 0) return NXF_OK;
+  const int64_t M = static_cast<int64_t>(p.n_lists) * p.k;
+  static const bool rank_merge = []() { const char* v = getenv("NXF_MERGE_SORTED"); return !(v && *v == '0'); }();
+  if (rank_merge && M <= kRankMergeMax) {
+    const size_t smem = static_cast<size_t>(M) * 16;
+    if (p.packed != nullptr) {
+      if (smem > 48 * 1024) { if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(merge_sorted_lists_kernel<true>), static_cast<int>(smem))) return rc; }
+      merge_sorted_lists_kernel<true><<<static_cast<unsigned>(p.nq), 128, smem, stream>>>(p);
+    } else {
+      if (smem > 48 * 1024) { if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(merge_sorted_lists_kernel<false>), static_cast<int>(smem))) return rc; }
+      merge_sorted_lists_kernel<false><<<static_cast<unsigned>(p.nq), 128, smem, stream>>>(p);
+    }
+    NXF_CUDA(cudaGetLastError());
+    return NXF_OK;
+  }
   if (p.packed != nullptr) merge_lists_kernel<true><<<static_cast<unsigned>(p.nq), mg::THREADS, 0, stream>>>(p);
   else merge_lists_kernel<false><<<static_cast<unsigned>(p.nq), mg::THREADS, 0, stream>>>(p);
   NXF_CUDA(cudaGetLastError());

@@ -176,3 +176,43 @@ def test_packed_search_and_merge_on_logical_shards():
         assert rep.ok, (metric, store, rep.messages[:5])
         last = lists[3].cpu().numpy().view([("score", "<f4"), ("row", "<i4")])
         assert (last["row"][:, 25:] == -1).all() and (last["row"][:, :25] >= 0).all() and (last["row"][:, :25] < 25).all()   # shard-local rows
+
+
+@pytest.mark.parametrize("G,k,k_out,metric", [(2, 100, 100, "ip"), (8, 500, 500, "ip"), (9, 500, 100, "ip"), (8, 100, 37, "l2"), (3, 7, 7, "ip"), (64, 60, 60, "ip")])
+def test_merge_kernels_on_sorted_lists_with_ties_and_padding(G, k, k_out, metric):
+    """K3 in both forms (rank merge of sorted lists up to 4 096 entries per query, select + sort beyond) against a numpy merge:
+    equal scores across lists (order: ascending global id), lists shorter than k (-1 padding), fewer valid entries than k_out."""
+    import torch
+    from nexus_b200 import merge_topk
+    rng = np.random.default_rng(G * 1000 + k)
+    nq = 50
+    pool = np.round(rng.standard_normal(400), 2).astype(np.float32)           # few distinct values: many exact ties
+    S = np.empty((G, nq, k), np.float32)
+    I = np.empty((G, nq, k), np.int64)
+    sign = -1.0 if metric == "l2" else 1.0
+    for g in range(G):
+        for q in range(nq):
+            n_valid = k if (g + q) % 5 else int(rng.integers(0, k + 1))
+            sc = rng.choice(pool, size=k).astype(np.float32)
+            if metric == "l2":
+                sc = np.abs(sc)
+            ids = (rng.choice(10_000, size=k, replace=False) * G + g).astype(np.int64)   # disjoint id sets per list, like row shards
+            order = np.lexsort((ids, -sign * sc))
+            sc, ids = sc[order], ids[order]
+            sc[n_valid:] = -sign * np.finfo(np.float32).max
+            ids[n_valid:] = -1
+            S[g, q], I[g, q] = sc, ids
+    if nq > 3:
+        I[:, 3, :] = -1                                                          # a query without any valid entry
+        S[:, 3, :] = -sign * np.finfo(np.float32).max
+    D, J = merge_topk(torch.from_numpy(S).cuda(), torch.from_numpy(I).cuda(), k_out, metric)
+    D, J = D.cpu().numpy(), J.cpu().numpy()
+    for q in range(nq):
+        s, i = S[:, q].reshape(-1), I[:, q].reshape(-1)
+        ok = i >= 0
+        s, i = s[ok], i[ok]
+        order = np.lexsort((i, -sign * s))[:k_out]
+        m = len(order)
+        np.testing.assert_array_equal(J[q, :m], i[order])
+        np.testing.assert_array_equal(D[q, :m], s[order])
+        assert (J[q, m:] == -1).all() and (D[q, m:] == -sign * np.finfo(np.float32).max).all()
