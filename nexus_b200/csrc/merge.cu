@@ -15,21 +15,31 @@
 
 namespace nxf {
 
-// ---- arena merge (+ optional rescore) ---------------------------------------------------------
+// ---- arena merge (+ optional rescore, certificate) -------------------------------------------
+// Round 2 (the kernel is what a row shard pays on top of its GEMM and does not shrink with the shard):
+//   * slices of <= 2 048 entries are staged in shared memory once; the selection passes run there instead of over global memory;
+//   * with a certificate, only candidates that can still reach the top-k are re-scored: k candidates have a pass score >= a_k (the
+//     k-th largest pass score), so the true k-th score is >= a_k - eps, and a candidate whose pass score is below a_k - 2 eps cannot
+//     beat it -- it is dropped before the gather (C2: ~150 of the k' = 200 rows per query are read);
+//   * four candidate rows in flight per warp instead of two;
+//   * up to 512 survivors are ordered by counting (rank = number of larger keys; one barrier) instead of a bitonic network.
+namespace mg { constexpr int STAGE = 2048; constexpr int RANK_SORT_MAX = 512; }
+
 template <typename T>
 __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaParams p) {
   extern __shared__ __align__(16) unsigned char dyn_smem[];
-  uint64_t* keys = reinterpret_cast<uint64_t*>(dyn_smem);            // [MAXK]
-  float* q_s = reinterpret_cast<float*>(dyn_smem + mg::MAXK * 8);    // [dim] when rescore / L2
+  uint64_t* keys = reinterpret_cast<uint64_t*>(dyn_smem);                       // [MAXK] sort keys; first the selected entries
+  Entry* stage = reinterpret_cast<Entry*>(dyn_smem + mg::MAXK * 8);             // [STAGE] the staged slice, later the live candidates
+  float* q_s = reinterpret_cast<float*>(dyn_smem + mg::MAXK * 8 + mg::STAGE * 8);  // [ld] when rescore / L2
   __shared__ uint32_t hist[256];
   __shared__ uint32_t sh_prefix;
-  __shared__ int sh_need, sh_gt, sh_eq;
-  __shared__ float sh_qnorm, sh_tau_min;
+  __shared__ int sh_need, sh_gt, sh_eq, sh_live;
+  __shared__ float sh_qnorm, sh_tau_min, sh_sk;
   __shared__ float red[mg::THREADS / 32];
 
   const int64_t qi = blockIdx.x;
   const int tid = threadIdx.x;
-  const Entry* __restrict__ src = p.arena + qi * p.arena_stride;
+  const Entry* __restrict__ gsrc = p.arena + qi * p.arena_stride;
   int64_t m64 = p.qcnt[qi];
   if (m64 > p.arena_stride) m64 = p.arena_stride;
   const int M = static_cast<int>(m64);
@@ -44,7 +54,6 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
       q_s[d] = v;
       part += v * v;
     }
-    // block reduce |q|^2 (the L2 output and the certificate need it)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(kFullMask, part, o);
     if ((tid & 31) == 0) red[tid >> 5] = part;
@@ -55,16 +64,20 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
       sh_qnorm = s;
     }
   }
-  if (tid == 0) { sh_gt = 0; sh_eq = 0; }
+  const bool staged = M <= mg::STAGE;
+  if (staged) for (int i = tid; i < M; i += mg::THREADS) stage[i] = gsrc[i];
+  if (tid == 0) { sh_gt = 0; sh_eq = 0; sh_live = 0; sh_sk = 0.f; }
   __syncthreads();
 
+  // ---- the k' best by pass score -> ent[0, keep) ----
   if (M > keep) {
-    block_radix_select(M, keep, [&](int i) { return okey(src[i].score); }, hist, &sh_prefix, &sh_need);
+    if (staged) block_radix_select(M, keep, [&](int i) { return okey(stage[i].score); }, hist, &sh_prefix, &sh_need);
+    else block_radix_select(M, keep, [&](int i) { return okey(gsrc[i].score); }, hist, &sh_prefix, &sh_need);
     const uint32_t kth = sh_prefix;
     const int need = sh_need;
     const int n_gt = keep - need;
     for (int i = tid; i < M; i += mg::THREADS) {
-      const Entry e = src[i];
+      const Entry e = staged ? stage[i] : gsrc[i];
       const uint32_t key = okey(e.score);
       if (key > kth) {
         ent[atomicAdd(&sh_gt, 1)] = e;
@@ -74,17 +87,17 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
       }
     }
   } else {
-    for (int i = tid; i < M; i += mg::THREADS) ent[i] = src[i];
+    for (int i = tid; i < M; i += mg::THREADS) ent[i] = staged ? stage[i] : gsrc[i];
   }
   __syncthreads();
 
   // ---- certificate, first half: tau' = the smallest PASS score among the kept candidates bounds the pass score of every other row ----
+  float eps = 0.f;
   if (p.cert) {
     float mn = INFINITY;
     for (int i = tid; i < keep; i += mg::THREADS) mn = fminf(mn, ent[i].score);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(kFullMask, mn, o));
-    __syncthreads();  // red[] is free again (|q|^2 was folded before the previous barrier)
     if ((tid & 31) == 0) red[tid >> 5] = mn;
     __syncthreads();
     if (tid == 0) {
@@ -92,90 +105,141 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
       for (int w = 1; w < mg::THREADS / 32; ++w) m = fminf(m, red[w]);
       sh_tau_min = m;
     }
+    eps = (p.eps_rel * sqrtf(sh_qnorm) + p.eps_abs) * sqrtf(__uint_as_float(*p.max_norm2)) * 1.0001f;
   }
 
-  // ---- exact fp32 re-score: one warp per candidate, two candidates in flight per warp, 16-byte loads ----
+  // ---- the candidates worth re-scoring -> live[0, n_live) ----
+  Entry* live = ent;
+  int n_live = keep;
+  if (p.rescore && p.cert && keep > p.k_out) {
+    block_radix_select(keep, p.k_out, [&](int i) { return okey(ent[i].score); }, hist, &sh_prefix, &sh_need);
+    const float floor_s = okey_inv(sh_prefix) - 2.f * eps;     // a_k - 2 eps
+    for (int i = tid; i < keep; i += mg::THREADS) {
+      const Entry e = ent[i];
+      if (e.score >= floor_s) stage[atomicAdd(&sh_live, 1)] = e;
+    }
+    __syncthreads();
+    live = stage;
+    n_live = sh_live;
+  }
+
+  // ---- exact fp32 re-score: one warp per candidate, four candidates in flight per warp, 16-byte loads ----
   // (rows are ld = 64k elements long and zero padded, q_s holds ld entries: no tail handling)
   if (p.rescore) {
     const T* __restrict__ corpus = reinterpret_cast<const T*>(p.corpus);
     const int warp = tid >> 5, lane = tid & 31;
     const int ld = static_cast<int>(p.ld);
     constexpr int NW = mg::THREADS / 32;
-    for (int c = warp; c < keep; c += 2 * NW) {
-      const int c2 = c + NW;
-      const bool two = c2 < keep;
-      const T* r0 = corpus + static_cast<int64_t>(ent[c].row) * p.ld;
-      const T* r1 = corpus + static_cast<int64_t>(ent[two ? c2 : c].row) * p.ld;
-      float dot0 = 0.f, nn0 = 0.f, dot1 = 0.f, nn1 = 0.f;
+    constexpr int RIF = 4;  // rows in flight per warp
+    for (int c0 = warp; c0 < n_live; c0 += RIF * NW) {
+      const T* r[RIF];
+      bool on[RIF];
+      float dot[RIF], nn[RIF];
+#pragma unroll
+      for (int u = 0; u < RIF; ++u) {
+        const int c = c0 + u * NW;
+        on[u] = c < n_live;
+        r[u] = corpus + static_cast<int64_t>(live[on[u] ? c : c0].row) * p.ld;
+        dot[u] = 0.f; nn[u] = 0.f;
+      }
       for (int d0 = lane * 8; d0 < ld; d0 += 256) {
-        float a[8], b[8];
-        load8_f32<T>(r0 + d0, a);
-        load8_f32<T>(r1 + d0, b);
+        float x[RIF][8];
+#pragma unroll
+        for (int u = 0; u < RIF; ++u) load8_f32<T>(r[u] + d0, x[u]);
         const float4 q0 = *reinterpret_cast<const float4*>(q_s + d0), q1 = *reinterpret_cast<const float4*>(q_s + d0 + 4);
         const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          dot0 = fmaf(qv[e], a[e], dot0); nn0 = fmaf(a[e], a[e], nn0);
-          dot1 = fmaf(qv[e], b[e], dot1); nn1 = fmaf(b[e], b[e], nn1);
-        }
+        for (int u = 0; u < RIF; ++u)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { dot[u] = fmaf(qv[e], x[u][e], dot[u]); nn[u] = fmaf(x[u][e], x[u][e], nn[u]); }
       }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        dot0 += __shfl_xor_sync(kFullMask, dot0, o); nn0 += __shfl_xor_sync(kFullMask, nn0, o);
-        dot1 += __shfl_xor_sync(kFullMask, dot1, o); nn1 += __shfl_xor_sync(kFullMask, nn1, o);
-      }
-      if (lane == 0) {
-        ent[c].score = (p.metric == NXF_METRIC_L2) ? (dot0 - 0.5f * nn0) : dot0;
-        if (two) ent[c2].score = (p.metric == NXF_METRIC_L2) ? (dot1 - 0.5f * nn1) : dot1;
+      for (int u = 0; u < RIF; ++u) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { dot[u] += __shfl_xor_sync(kFullMask, dot[u], o); nn[u] += __shfl_xor_sync(kFullMask, nn[u], o); }
+        if (lane == 0 && on[u]) live[c0 + u * NW].score = (p.metric == NXF_METRIC_L2) ? (dot[u] - 0.5f * nn[u]) : dot[u];
       }
     }
-    __syncthreads();
   }
+  __syncthreads();
 
-  // ---- sort by (score desc, row asc) ----
-  const int P = next_pow2(max(keep, 2));
-  // ent[] aliases keys[] slot for slot (8 bytes each): every thread rewrites only the slots it reads
-  for (int i = tid; i < P; i += mg::THREADS) {
-    uint64_t kk = 0;  // below every real key
-    if (i < keep) { const Entry e = ent[i]; kk = sort_key(e.score, e.row); }
-    keys[i] = kk;
-  }
-  block_bitonic_desc<false>(keys, nullptr, P);
-
-  // ---- certificate, second half: the re-scored k-th score must clear tau' + eps (params.cuh, MergeArenaParams::cert) ----
-  if (p.cert && tid == 0) {
-    bool pass = static_cast<int64_t>(keep) >= p.n_rows;     // every row of the index was a candidate
-    if (!pass && keep >= p.k_out) {
-      const float s_k = sort_key_score(keys[p.k_out - 1]);
-      const float mx = __uint_as_float(*p.max_norm2);
-      const float eps = (p.eps_rel * sqrtf(sh_qnorm) + p.eps_abs) * sqrtf(mx) * 1.0001f;
-      pass = s_k >= sh_tau_min + eps;
-    }
-    p.cert_fail[qi] = pass ? 0u : 1u;
-    if (!pass) atomicAdd(p.cert_count, 1u);
-  }
-
+  // ---- order by (score desc, row asc) and write ----
   const float qn = (p.metric == NXF_METRIC_L2) ? sh_qnorm : 0.f;
-  for (int j = tid; j < p.k_out; j += mg::THREADS) {
-    float s;
-    int64_t id;
-    if (j < keep) {
-      const uint64_t kk = keys[j];
-      const float sc = sort_key_score(kk);
-      s = (p.metric == NXF_METRIC_L2) ? fmaxf(qn - 2.f * sc, 0.f) : sc;
-      id = static_cast<int64_t>(sort_key_row(kk)) + p.id_offset;
-    } else {
-      s = (p.metric == NXF_METRIC_L2) ? FLT_MAX : -FLT_MAX;
-      id = -1;
-    }
+  auto emit = [&](int j, uint64_t kk) {
+    const float sc = sort_key_score(kk);
+    const float s = (p.metric == NXF_METRIC_L2) ? fmaxf(qn - 2.f * sc, 0.f) : sc;
+    const int32_t row = sort_key_row(kk);
     if (p.out_packed != nullptr) {
-      Entry e;
-      e.score = s;
-      e.row = id < 0 ? -1 : static_cast<int32_t>(id - p.id_offset);  // shard-local: the merge adds the shard's offset
+      Entry e; e.score = s; e.row = row;                     // shard-local: the shard merge adds the shard's offset
       p.out_packed[qi * p.k_out + j] = e;
     } else {
       p.out_scores[qi * p.k_out + j] = s;
-      p.out_ids[qi * p.k_out + j] = id;
+      p.out_ids[qi * p.k_out + j] = static_cast<int64_t>(row) + p.id_offset;
+    }
+  };
+  const int n_out = min(n_live, p.k_out);
+  if (n_live <= mg::RANK_SORT_MAX) {
+    // counting sort: keys are distinct (rows are), the rank of a key is the number of larger ones
+    uint64_t mine[mg::RANK_SORT_MAX / mg::THREADS];
+#pragma unroll
+    for (int u = 0; u < mg::RANK_SORT_MAX / mg::THREADS; ++u) {
+      const int i = tid + u * mg::THREADS;
+      mine[u] = 0;
+      if (i < n_live) { const Entry e = live[i]; mine[u] = sort_key(e.score, e.row); }
+    }
+    __syncthreads();   // every thread has read its entries of live[] (which may alias keys[])
+#pragma unroll
+    for (int u = 0; u < mg::RANK_SORT_MAX / mg::THREADS; ++u) {
+      const int i = tid + u * mg::THREADS;
+      if (i < n_live) keys[i] = mine[u];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < mg::RANK_SORT_MAX / mg::THREADS; ++u) {
+      const int i = tid + u * mg::THREADS;
+      if (i >= n_live) continue;
+      int rank = 0;
+      for (int j = 0; j < n_live; ++j) rank += (keys[j] > mine[u]) ? 1 : 0;
+      if (rank < p.k_out) emit(rank, mine[u]);
+      if (rank == p.k_out - 1) sh_sk = sort_key_score(mine[u]);
+    }
+  } else {
+    const int P = next_pow2(max(n_live, 2));
+    uint64_t tmp[mg::MAXK / mg::THREADS];
+#pragma unroll
+    for (int u = 0; u < mg::MAXK / mg::THREADS; ++u) {
+      const int i = tid + u * mg::THREADS;
+      tmp[u] = 0;  // below every real key
+      if (i < n_live) { const Entry e = live[i]; tmp[u] = sort_key(e.score, e.row); }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < mg::MAXK / mg::THREADS; ++u) {
+      const int i = tid + u * mg::THREADS;
+      if (i < P) keys[i] = tmp[u];
+    }
+    block_bitonic_desc<false>(keys, nullptr, P);
+    for (int j = tid; j < n_out; j += mg::THREADS) emit(j, keys[j]);
+    if (tid == 0 && n_live >= p.k_out) sh_sk = sort_key_score(keys[p.k_out - 1]);
+  }
+  for (int j = n_out + tid; j < p.k_out; j += mg::THREADS) {
+    if (p.out_packed != nullptr) {
+      Entry e; e.score = (p.metric == NXF_METRIC_L2) ? FLT_MAX : -FLT_MAX; e.row = -1;
+      p.out_packed[qi * p.k_out + j] = e;
+    } else {
+      p.out_scores[qi * p.k_out + j] = (p.metric == NXF_METRIC_L2) ? FLT_MAX : -FLT_MAX;
+      p.out_ids[qi * p.k_out + j] = -1;
+    }
+  }
+
+  // ---- certificate, second half: the re-scored k-th score must clear tau' + eps (params.cuh, MergeArenaParams::cert) ----
+  if (p.cert) {
+    __syncthreads();
+    if (tid == 0) {
+      bool pass = static_cast<int64_t>(keep) >= p.n_rows;     // every row of the index was a candidate
+      if (!pass && n_live >= p.k_out) pass = sh_sk >= sh_tau_min + eps;
+      p.cert_fail[qi] = pass ? 0u : 1u;
+      if (!pass) atomicAdd(p.cert_count, 1u);
     }
   }
 }
@@ -183,7 +247,7 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream) {
   if (nq <= 0) return NXF_OK;
   const bool need_q = p.rescore || p.metric == NXF_METRIC_L2;
-  const size_t smem = static_cast<size_t>(mg::MAXK) * 8 + (need_q ? static_cast<size_t>(p.ld) * 4 : 0);
+  const size_t smem = static_cast<size_t>(mg::MAXK) * 8 + static_cast<size_t>(mg::STAGE) * 8 + (need_q ? static_cast<size_t>(p.ld) * 4 : 0);
   if (smem > 200 * 1024) { set_error("merge: dim %d too large for the re-score stage", p.dim); return NXF_EUNSUPPORTED; }
 #define NXF_LAUNCH_MERGE(T)                                                                                          \
   do {                                                                                                               \
