@@ -1009,6 +1009,7 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
       kp.epi_sets = P.epi_sets;
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
+      kp.est_only = 0;
       kp.sink = sink;
       kp.round_tiles = P.round_tiles; kp.sync_window = P.sync_window;
       // the last launch of a multi-batch search may hold fewer query tiles than planned: never more clusters than tile-units
@@ -1049,11 +1050,10 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
           passes[n_pass++] = {0, P.n_tiles, P.k_fetch, 0};
         }
       }
-      const int user_debug = kp.debug;
       for (int ps = 0; ps < n_pass; ++ps) {
         kp.tile_begin = passes[ps].begin; kp.tile_end = passes[ps].end;
         kp.sink.k = passes[ps].k;
-        kp.debug = user_debug | (passes[ps].est_only ? 128 : 0);
+        kp.est_only = passes[ps].est_only;
         kp.sync_ctr = tau_g + 2 * nq_pad + ps;   // one round counter per pass (all zeroed above)
         rc = launch_k1(c_dt, P.cta_group, q16, bn, q16_ld, c_rows, c_rows2, idx->ld, kp, grid, stream);
         if (rc) return rc;
@@ -1064,7 +1064,7 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
           idx->stats.kernel_launches++;
         }
       }
-      kp.debug = user_debug;
+      kp.est_only = 0;
       if (n_pass > 1) {
         // verification + fall-back: the launch below returns at once unless some query holds fewer than min(k', n) candidates
         uint32_t* flag = tau_g + 2 * nq_pad + 8;

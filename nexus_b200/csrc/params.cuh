@@ -77,7 +77,8 @@ struct K1Params {
   uint32_t* sync_ctr;  // [1] zeroed per launch: rounds completed, summed over clusters
   const float* half_norm;
   uint32_t* prof;      // debug bit5: 4 x uint64 {prunes, prune cycles, end-merge cycles, warps} summed over epilogue warps
-  int debug;  // timing experiments: bit0 epilogue skips the selection; bit1 also skips the TMEM loads; bit2 producer issues no TMA;
+  int est_only;  // estimate-only pass: a slice that beats the row's threshold records its maximum instead of its scores
+  int debug;  // timing experiments (only in builds with -DNXF_K1_DEBUG_BUILD=1): bit0 epilogue skips the selection; bit1 also skips the TMEM loads; bit2 producer issues no TMA;
               // bit3 issuer issues no MMA; bit4 epilogue computes the maxima but never appends
   SinkParams sink;
 };

@@ -34,6 +34,14 @@
 
 namespace nxf {
 
+// Timing experiments (producer without loads, issuer without MMAs, epilogue without selection, prune counters; K1Params::debug) are
+// compiled in only with -DNXF_K1_DEBUG_BUILD=1 (NXF_EXTRA_NVCC_FLAGS, tools/k1_variants.sh): the shipped kernel carries none of
+// their tests in its hot loops (~1 % of stall samples each on three of them).
+#ifndef NXF_K1_DEBUG_BUILD
+#define NXF_K1_DEBUG_BUILD 0
+#endif
+#define NXF_K1_DBG(p_debug, bits) (NXF_K1_DEBUG_BUILD != 0 && ((p_debug) & (bits)) != 0)
+
 namespace k1 {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_N = 256;
@@ -89,7 +97,7 @@ __device__ __forceinline__ Entry ld_cg_entry(const Entry* p) {
 template <bool ADJ>
 __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbase, int32_t n_rows,
                                           const float* __restrict__ half_norm, EpiState& st, uint32_t* __restrict__ cand_words,
-                                          uint32_t my_first, int debug) {
+                                          uint32_t my_first, int debug, int est_only) {
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(vr[j]);
@@ -110,12 +118,12 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbas
     g[q4] = fmaxf(a, v[8 * q4 + 7]);
   }
   const float m = fmaxf(fmax3(g[0], g[1], g[2]), g[3]);
-  if (m > st.tau && !(debug & 16)) {
+  if (m > st.tau && !NXF_K1_DBG(debug, 16)) {
     const float tau = st.tau;
     // entry index in the candidate arena (uniform base + 32-bit index: one IMAD.WIDE per address); score and row go out
     // as two 32-bit stores so that no register pairing is forced on the accumulator values of the common path
     uint32_t w = my_first + static_cast<uint32_t>(st.cnt);
-    if (debug & 128) {
+    if (est_only) {
       // estimate-only pass: the slice maximum stands for the slice (its rank statistics bound the scores' from below)
       cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(m);
       cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(cbase);
@@ -236,7 +244,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 }
               }
               mbar_wait(&empty[s], ph ^ 1);
-              if (p.debug & 4) {  // pipeline timing only: no loads, the MMAs run on whatever the ring holds
+              if (NXF_K1_DBG(p.debug, 4)) {  // pipeline timing only: no loads, the MMAs run on whatever the ring holds
                 if (CG == 1 || rank == 0) mbar_arrive(&full[s]); else mbar_arrive_cluster(&full[s], 0);
               } else if (CG == 1) {
                 mbar_expect_tx(&full[s], C::STAGE_BYTES);
@@ -276,7 +284,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             tc_fence_after();
             const uint64_t a_desc = umma_desc_sw128(smem_u32(a_ptr(s)));
             const uint64_t b_desc = umma_desc_sw128(smem_u32(b_ptr(s)));
-            if (!(p.debug & 8)) {
+            if (!NXF_K1_DBG(p.debug, 8)) {
 #pragma unroll
               for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) {
                 // advance 16 elements = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
@@ -349,7 +357,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           // slow-path epilogue: the last corpus tile (rows past n are TMA zero fill) or the L2 metric
           const bool adj = (col0 + BLOCK_N > n_rows) || (p.half_norm != nullptr);
           const uint32_t tbase = taddr + as * BLOCK_N;
-          if (p.debug & 2) {
+          if (NXF_K1_DBG(p.debug, 2)) {
             // pipeline timing only: hand the accumulator back without reading it
             tc_fence_before();
             __syncwarp();
@@ -364,9 +372,9 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           for (int ch = 0; ch < BLOCK_N / 32; ch += 2) {
             tmem_ld_wait_dep(va);
             tmem_ld32(tbase + (ch + 1) * 32, vb);
-            if (!(p.debug & 1)) {
-              if (adj) epi_chunk<true>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
-              else epi_chunk<false>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
+            if (!NXF_K1_DBG(p.debug, 1)) {
+              if (adj) epi_chunk<true>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+              else epi_chunk<false>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
             }
             tmem_ld_wait_dep(vb);
             if (ch + 2 < BLOCK_N / 32) {
@@ -377,9 +385,9 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               __syncwarp();
               if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]); }
             }
-            if (!(p.debug & 1)) {
-              if (adj) epi_chunk<true>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
-              else epi_chunk<false>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug);
+            if (!NXF_K1_DBG(p.debug, 1)) {
+              if (adj) epi_chunk<true>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+              else epi_chunk<false>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
             }
           }
           // other owners' progress on this query: loaded during the previous tile, folded in only now so that its latency
@@ -390,10 +398,10 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           // published for the other owners of the query
           __syncwarp();  // this tile's appends (thread-private global stores) are visible to the warp
           unsigned need = __ballot_sync(kFullMask, cur.cnt > cap - BLOCK_N);
-          const bool prof = (p.debug & 32) && need;  // timing experiment: prune count / cycles per warp into the counter words
+          const bool prof = NXF_K1_DBG(p.debug, 32) && need;  // timing experiment: prune count / cycles per warp into the counter words
           const long long pc0 = prof ? clock64() : 0;
           const int pn = __popc(need);
-          if (need && !(p.debug & 64) && cur.cnt > cap - BLOCK_N) {
+          if (need && !NXF_K1_DBG(p.debug, 64) && cur.cnt > cap - BLOCK_N) {
             // the buffers were written tiles ago and may have left L2: every needy row pulls its own lines in now, so the serial
             // warp-cooperative prunes below find them there
             const char* b = reinterpret_cast<const char*>(warp_buf0 + static_cast<int64_t>(lane) * cap);
@@ -422,7 +430,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
     // ---- end of the launch (pass): every row's candidates (its sink.k best if it holds more) go to the query's arena slice ----
     __syncwarp();
-    const long long mc0 = (p.debug & 32) ? clock64() : 0;
+    const long long mc0 = NXF_K1_DBG(p.debug, 32) ? clock64() : 0;
 #pragma unroll 1
     for (int slot = 0; slot < 2; ++slot) {
       if (qt_base + slot >= p.num_qt) break;
@@ -449,7 +457,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         for (int i = lane; i < n; i += 32) dst[i] = buf[i];
       }
     }
-    if ((p.debug & 32) && lane == 0) {
+    if (NXF_K1_DBG(p.debug, 32) && lane == 0) {
       atomicAdd(reinterpret_cast<unsigned long long*>(p.prof) + 2, static_cast<unsigned long long>(clock64() - mc0));
       atomicAdd(reinterpret_cast<unsigned long long*>(p.prof) + 3, 1ull);
     }

@@ -81,12 +81,20 @@ def test_level_two_resolves_moderately_close_scores(store, nq):
 @pytest.mark.parametrize("store", ["f32", "bf16"])
 @pytest.mark.parametrize("mode,nq", [("numpy", 140), ("cuda", 140), ("packed", 140), ("numpy", 5), ("cuda", 3)])
 def test_near_duplicates_force_the_exact_level(store, mode, nq):
-    """1 000 near-copies of every query's best row (scores within 2e-5 of each other, some bit-equal): no bound separates rank k from
-    rank k', both certificates fail and the exact fp32 kernels decide.  Host buffers, device buffers and the packed (sharded) output."""
+    """Rows that no bound separates at rank k: 1 000 near-copies of every query's best row with scores within 2e-5 of each other
+    (fp32 storage), 400 bit-identical copies (16-bit storage, where the rounding of the stored rows spreads near-copies apart): both
+    certificates fail and the exact fp32 kernels decide.  Host buffers, device buffers and the packed (sharded) output."""
     import torch
     from nexus_b200 import FlatIndex, merge_packed
-    c, x = _near_duplicates(30000, 1000, 64, nq, 2e-5, seed=8)          # <= 16 failing queries: K2 (stream), more: KX (tile kernel)
-    c[-1] = c[-2]                                             # exact duplicates too
+    if store == "f32":
+        c, x = _near_duplicates(30000, 1000, 64, nq, 2e-5, seed=8)          # <= 16 failing queries: K2 (stream), more: KX (tile kernel)
+        c[-1] = c[-2]                                         # exact duplicates too
+    else:
+        rng = np.random.default_rng(8)
+        bg, x = gen_inputs(30000, 64, nq, seed=8)
+        best = oracle.round_to_bf16(0.9 * x + 0.01 * rng.standard_normal(x.shape).astype(np.float32))
+        c = np.concatenate([bg, np.repeat(best, 400, axis=0)], axis=0)
+        c = np.ascontiguousarray(c[rng.permutation(c.shape[0])])
     idx = FlatIndex(64, "ip", store)
     idx.add(c)
     if mode == "numpy":

@@ -213,6 +213,15 @@ def test_merge_kernels_on_sorted_lists_with_ties_and_padding(G, k, k_out, metric
         s, i = s[ok], i[ok]
         order = np.lexsort((i, -sign * s))[:k_out]
         m = len(order)
-        np.testing.assert_array_equal(J[q, :m], i[order])
         np.testing.assert_array_equal(D[q, :m], s[order])
+        if G * k <= 4096:
+            np.testing.assert_array_equal(J[q, :m], i[order])       # the rank merge: ties in ascending id order, always
+        else:
+            # select + sort: WHICH of the entries tied with the k_out-th score are kept is not defined (the reference's argsort
+            # and Faiss's heap do not define it either); every id must be a real entry with the reported score, none twice
+            score_of = dict(zip(i.tolist(), s.tolist()))
+            assert len(set(J[q, :m].tolist())) == m
+            assert all(score_of[int(a)] == float(b) for a, b in zip(J[q, :m], D[q, :m]))
+            inner = D[q, :m] != D[q, m - 1]
+            np.testing.assert_array_equal(J[q, :m][inner], i[order][inner])
         assert (J[q, m:] == -1).all() and (D[q, m:] == -sign * np.finfo(np.float32).max).all()
