@@ -334,6 +334,219 @@ int pool_workspace(size_t part_bytes, cudaStream_t stream, unsigned char** out) 
 }
 }  // namespace
 
+// ---- mean pooling as a persistent TMA stream (round 2) ---------------------------------------------
+// The split kernel above runs ~2 000 short CTAs whose fixed path (mask scan -> first loads -> shared-memory reduce -> fence -> atomic)
+// is as long as their streaming time: 0.38-0.46 of the HBM peak on the reference's default encode batch (256 x 512 x 768 f16).
+// Here ONE CTA per SM stays resident and a producer warp keeps a ring of shared-memory stages full with cp.async.bulk copies --
+// the positions of a row are contiguous in [B, L, H], so a chunk of positions is one contiguous block -- while eight consumer
+// warps accumulate from shared memory.  Work = segments (row b, slice sp of `splits`), fetched from a global counter by the
+// producer, which also scans the segment's mask (first / last unmasked position, weights) while earlier chunks are in flight: the
+// per-segment fixed costs overlap the stream instead of serialising with it.  splits == 1: the CTA finalises the row itself (no
+// workspace traffic); splits > 1: partial sums + last-arriver finalisation as in the split kernel (same fixed summation order).
+namespace k0s {
+constexpr int CONSUMER_WARPS = 8;
+constexpr int CONSUMERS = CONSUMER_WARPS * 32;
+constexpr int THREADS = CONSUMERS + 32;
+constexpr int MAX_STAGES = 8;
+constexpr int MAX_CH = 32;  // positions per stage (one producer lane per position)
+struct __align__(16) StageMeta {
+  int seg;        // segment id, -1 = no more work
+  int npos;       // positions in this stage
+  int last;       // last stage of its segment
+  int pad;
+  unsigned long long wsum;  // (last stage) sum of the segment's mask words
+  float w[MAX_CH];
+};
+}  // namespace k0s
+
+template <typename T, typename O, int VEC>
+__global__ void __launch_bounds__(k0s::THREADS, 1) pool_mean_stream_kernel(const T* __restrict__ hidden, const int64_t* __restrict__ mask, int64_t B,
+                                                                          int64_t L, int64_t H, int normalize, float eps, O* __restrict__ out,
+                                                                          int splits, int CH, int stages, int G, float* __restrict__ partial,
+                                                                          unsigned long long* __restrict__ den_g, unsigned int* __restrict__ counter,
+                                                                          unsigned int* __restrict__ work_ctr, unsigned int* __restrict__ exit_ctr) {
+  using namespace k0s;
+  extern __shared__ __align__(128) unsigned char sm[];
+  const int64_t row_bytes = H * static_cast<int64_t>(sizeof(T));
+  const int64_t stage_bytes = (row_bytes * CH + 127) / 128 * 128;
+  unsigned char* ring = sm;
+  StageMeta* meta = reinterpret_cast<StageMeta*>(ring + stage_bytes * stages);
+  uint64_t* full = reinterpret_cast<uint64_t*>(meta + MAX_STAGES);
+  uint64_t* empty = full + MAX_STAGES;
+  float* vals = reinterpret_cast<float*>(empty + MAX_STAGES);   // [G][H], reused as [H]
+  __shared__ float red_f[CONSUMER_WARPS];
+  __shared__ unsigned int s_last;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const unsigned lane = tid & 31;
+  const int64_t n_seg = B * splits;
+  const int64_t lc = (L + splits - 1) / splits;
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], CONSUMER_WARPS); }
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  if (warp == CONSUMER_WARPS) {
+    // ------------------------------- producer warp -------------------------------
+    int s = 0;
+    uint32_t ph = 0;
+    for (;;) {
+      unsigned int seg = 0;
+      if (lane == 0) seg = atomicAdd(work_ctr, 1u);
+      seg = __shfl_sync(0xFFFFFFFFu, seg, 0);
+      if (static_cast<int64_t>(seg) >= n_seg) {
+        mbar_wait(&empty[s], ph ^ 1);
+        if (lane == 0) { meta[s].seg = -1; meta[s].npos = 0; meta[s].last = 0; }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[s]);
+        break;
+      }
+      const int64_t b = seg / splits;
+      const int sp = static_cast<int>(seg - b * splits);
+      const int64_t l0 = sp * lc, l1 = min(L, l0 + lc);
+      const int64_t* mb = mask + b * L;
+      unsigned long long wsum = 0;
+      int lo = INT_MAX, hi = -1;
+      for (int64_t l = l0 + lane; l < l1; l += 32) {
+        const int64_t w = mb[l];
+        wsum += static_cast<unsigned long long>(w);
+        if (w != 0) { lo = min(lo, static_cast<int>(l - l0)); hi = max(hi, static_cast<int>(l - l0)); }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xFFFFFFFFu, wsum, o);
+      lo = __reduce_min_sync(0xFFFFFFFFu, lo);
+      hi = __reduce_max_sync(0xFFFFFFFFu, hi);
+      const int64_t n0 = (hi >= 0) ? l0 + lo : l0, n1 = (hi >= 0) ? l0 + hi + 1 : l0;   // empty when the whole segment is masked
+      const unsigned char* hb = reinterpret_cast<const unsigned char*>(hidden + b * L * H);
+      int64_t p0 = n0;
+      do {
+        const int np = static_cast<int>(min(static_cast<int64_t>(CH), n1 - p0));
+        const bool last = p0 + np >= n1;
+        mbar_wait(&empty[s], ph ^ 1);
+        if (static_cast<int>(lane) < np) meta[s].w[lane] = static_cast<float>(mb[p0 + lane]);
+        if (lane == 0) { meta[s].seg = static_cast<int>(seg); meta[s].npos = np; meta[s].last = last ? 1 : 0; meta[s].wsum = wsum; }
+        __syncwarp();
+        if (lane == 0) {
+          if (np > 0) {
+            const uint32_t bytes = static_cast<uint32_t>(np * row_bytes);
+            mbar_expect_tx(&full[s], bytes);
+            bulk_load_1d(ring + s * stage_bytes, hb + p0 * row_bytes, bytes, &full[s]);
+          } else {
+            mbar_arrive(&full[s]);
+          }
+        }
+        if (++s == stages) { s = 0; ph ^= 1; }
+        p0 += np;
+      } while (p0 < n1);
+    }
+    // the last producer to leave puts the two scheduling words back to zero for the next launch on this workspace
+    if (lane == 0) {
+      __threadfence();
+      if (atomicAdd(exit_ctr, 1u) == gridDim.x - 1) { *work_ctr = 0u; *exit_ctr = 0u; __threadfence(); }
+    }
+    return;
+  }
+
+  // ------------------------------------ consumers ------------------------------------
+  const int nvec = static_cast<int>(H / VEC);
+  const int g = tid / nvec, v = tid - g * nvec;
+  const bool active = g < G;
+  float acc[VEC];
+#pragma unroll
+  for (int e = 0; e < VEC; ++e) acc[e] = 0.f;
+  int s = 0;
+  uint32_t ph = 0;
+  for (;;) {
+    mbar_wait(&full[s], ph);
+    const int seg = meta[s].seg;
+    const int npos = meta[s].npos;
+    const int last = meta[s].last;
+    const unsigned long long wsum = meta[s].wsum;
+    if (active) {
+      const T* st = reinterpret_cast<const T*>(ring + s * stage_bytes) + static_cast<int64_t>(v) * VEC;
+#pragma unroll 4
+      for (int pp = g; pp < npos; pp += G) {
+        float x[VEC];
+        VecLoad<T, VEC>::load(st + static_cast<int64_t>(pp) * H, x);
+        const float wf = meta[s].w[pp];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) acc[e] = fmaf(x[e], wf, acc[e]);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+    if (++s == stages) { s = 0; ph ^= 1; }
+    if (seg < 0) break;
+    if (!last) continue;
+
+    // ---- end of a segment ----
+    const int64_t b = seg / splits;
+    const int sp = seg - static_cast<int>(b) * splits;
+    if (active) {
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) { vals[static_cast<int64_t>(g) * H + v * VEC + e] = acc[e]; acc[e] = 0.f; }
+    }
+    asm volatile("barrier.cta.sync.aligned 1, %0;" ::"n"(CONSUMERS) : "memory");
+    float fden;
+    if (splits == 1) {
+      for (int64_t h = tid; h < H; h += CONSUMERS) {
+        float t = 0.f;
+        for (int gg = 0; gg < G; ++gg) t += vals[static_cast<int64_t>(gg) * H + h];
+        vals[h] = t;   // group 0's slot: only this thread reads and writes column h
+      }
+      fden = static_cast<float>(static_cast<long long>(wsum));
+    } else {
+      float* my_part = partial + (b * splits + sp) * H;
+      for (int64_t h = tid; h < H; h += CONSUMERS) {
+        float t = 0.f;
+        for (int gg = 0; gg < G; ++gg) t += vals[static_cast<int64_t>(gg) * H + h];
+        my_part[h] = t;
+      }
+      __threadfence();
+      asm volatile("barrier.cta.sync.aligned 1, %0;" ::"n"(CONSUMERS) : "memory");
+      if (tid == 0) {
+        if (wsum != 0) atomicAdd(&den_g[b], wsum);
+        __threadfence();
+        s_last = (atomicAdd(&counter[b], 1u) == static_cast<unsigned>(splits - 1)) ? 1u : 0u;
+      }
+      asm volatile("barrier.cta.sync.aligned 1, %0;" ::"n"(CONSUMERS) : "memory");
+      if (!s_last) continue;
+      __threadfence();
+      fden = static_cast<float>(static_cast<long long>(*reinterpret_cast<volatile unsigned long long*>(&den_g[b])));
+      for (int64_t h = tid; h < H; h += CONSUMERS) {
+        float t = 0.f;
+        for (int j = 0; j < splits; ++j) t += __ldcg(partial + (b * splits + j) * H + h);
+        vals[h] = t;
+      }
+    }
+    // divide, normalise, cast, store (vals[h] is touched by thread h % CONSUMERS only until the barrier below)
+    float ss = 0.f;
+    for (int64_t h = tid; h < H; h += CONSUMERS) {
+      const float t = vals[h] / fden;  // 0/0 -> NaN for an empty mask, like the reference
+      vals[h] = t;
+      ss = fmaf(t, t, ss);
+    }
+    float scale = 1.f;
+    if (normalize) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xFFFFFFFFu, ss, o);
+      if (lane == 0) red_f[warp] = ss;
+      asm volatile("barrier.cta.sync.aligned 1, %0;" ::"n"(CONSUMERS) : "memory");
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < CONSUMER_WARPS; ++w) tot += red_f[w];
+      const float nrm = sqrtf(tot);
+      scale = 1.f / (eps > 0.f ? fmaxf(nrm, eps) : nrm);
+    }
+    O* ob = out + b * H;
+    for (int64_t h = tid; h < H; h += CONSUMERS) ob[h] = from_f32<O>(normalize ? vals[h] * scale : vals[h]);
+    if (splits > 1 && tid == 0) { den_g[b] = 0ull; counter[b] = 0u; }   // leave the row's control words as they were found
+    asm volatile("barrier.cta.sync.aligned 1, %0;" ::"n"(CONSUMERS) : "memory");   // vals / red_f free for the next segment
+  }
+}
+
 template <typename T, typename O, int VEC>
 static int launch_pool_mean_split(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int normalize, float eps,
                                   void* out, cudaStream_t stream) {
@@ -377,13 +590,67 @@ static int launch_pool_mean_split(const void* hidden, const int64_t* mask, int64
   return NXF_OK;
 }
 
+// Returns NXF_OK after launching, or 1 when the shape does not fit the stream kernel (the caller falls back to the split kernel).
+template <typename T, typename O, int VEC>
+static int launch_pool_mean_stream(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int normalize, float eps,
+                                   void* out, cudaStream_t stream) {
+  using namespace k0s;
+  const int nvec = static_cast<int>(H / VEC);
+  if (nvec > CONSUMERS || B >= 65535) return 1;
+  const int G = std::max(1, CONSUMERS / nvec);
+  const int64_t row_bytes = H * static_cast<int64_t>(sizeof(T));
+  const int CH = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(MAX_CH, 32768 / row_bytes)));
+  const int64_t stage_bytes = (row_bytes * CH + 127) / 128 * 128;
+  const int64_t fixed = static_cast<int64_t>(MAX_STAGES) * sizeof(StageMeta) + 2 * MAX_STAGES * 8 + static_cast<int64_t>(G) * H * 4 + 256;
+  const int stages = static_cast<int>(std::min<int64_t>(MAX_STAGES, (200 * 1024 - fixed) / stage_bytes));
+  if (stages < 3) return 1;
+  int dev = 0, sms = 148;
+  NXF_CUDA(cudaGetDevice(&dev));
+  static int sm_cache[32] = {0};
+  if (dev >= 0 && dev < 32) {
+    if (sm_cache[dev] == 0) NXF_CUDA(cudaDeviceGetAttribute(&sm_cache[dev], cudaDevAttrMultiProcessorCount, dev));
+    sms = sm_cache[dev];
+  }
+  // segments: at least ~6 per CTA for the dynamic schedule to balance ragged masks, each at least two stages long
+  int splits = 1;
+  while (B * splits < 6 * static_cast<int64_t>(sms) && L / (2 * splits) >= 2 * CH && splits < 1024) splits *= 2;
+  const size_t part_bytes = splits > 1 ? static_cast<size_t>(B) * splits * H * 4 : 0;
+  unsigned char* ws = nullptr;
+  int rc = pool_workspace(part_bytes, stream, &ws);
+  if (rc) return rc;
+  unsigned long long* den = reinterpret_cast<unsigned long long*>(ws);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(ws + size_t(65536) * 8);
+  unsigned int* sched = reinterpret_cast<unsigned int*>(den + 65535);   // row 65 535 never exists: its den word holds the two scheduling counters
+  float* partial = reinterpret_cast<float*>(ws + kPoolCtlBytes);
+  const size_t smem = static_cast<size_t>(stage_bytes) * stages + fixed;
+  auto kern = pool_mean_stream_kernel<T, O, VEC>;
+  if (int r2 = ensure_dyn_smem(reinterpret_cast<const void*>(kern), static_cast<int>(smem))) return r2;
+  const int grid = static_cast<int>(std::min<int64_t>(sms, B * splits));
+  kern<<<grid, THREADS, smem, stream>>>((const T*)hidden, mask, B, L, H, normalize, eps, (O*)out, splits, CH, stages, G, partial, den, counter,
+                                       sched, sched + 1);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
 template <typename T, typename O, int VEC>
 static int launch_pool_t(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int pooling, int normalize, float eps,
                          void* out, cudaStream_t stream) {
   const int nvec = static_cast<int>(H / VEC);
   // mean over vectorisable rows: the split kernel (any B fills the GPU); B <= 65535 is the grid's y limit
   if (pooling == NXF_POOL_MEAN && VEC > 1 && nvec <= 512 && B <= 65535 && static_cast<size_t>(std::max(1, 512 / nvec)) * H * 4 <= 160 * 1024)
+  {
+    if constexpr (VEC > 1) {
+      // the persistent TMA stream first (NXF_POOL_STREAM=0: the split kernel, for A/B timing); it needs the cached workspace
+      const char* se = getenv("NXF_POOL_STREAM");
+      const char* we = getenv("NXF_POOL_WS_CACHE");
+      const bool ws_cached = we ? atoi(we) != 0 : NXF_POOL_WS_CACHE_DEFAULT != 0;
+      if (!(se && *se == '0') && ws_cached) {
+        const int rc = launch_pool_mean_stream<T, O, VEC>(hidden, mask, B, L, H, normalize, eps, out, stream);
+        if (rc <= 0) return rc;
+      }
+    }
     return launch_pool_mean_split<T, O, VEC>(hidden, mask, B, L, H, normalize, eps, out, stream);
+  }
   int groups = 1;
   if (pooling == NXF_POOL_MEAN) {
     groups = std::max(1, std::min(k0::MAX_GROUPS, k0::THREADS / std::max(1, std::min(nvec, k0::THREADS))));
