@@ -390,56 +390,110 @@ __global__ void __launch_bounds__(k0s::THREADS, 1) pool_mean_stream_kernel(const
 
   if (warp == CONSUMER_WARPS) {
     // ------------------------------- producer warp -------------------------------
+    // Work is walked as (segment, sub-block) pairs; a sub-block = up to 32 * MR positions whose mask words the warp holds in
+    // registers (lane j: positions base + j + 32 r).  The NEXT pair's mask words are loaded before the current pair's chunks are
+    // pushed, so the producer never waits for a mask load between two bulk copies (a first version read the weights of every
+    // chunk from global memory right before its copy: ~0.7 us per chunk, twice the chunk's HBM time).
+    constexpr int MR = 8;
+    const int SB = (32 * MR / CH) * CH;   // positions per sub-block: a multiple of the chunk, so chunks never straddle sub-blocks
     int s = 0;
     uint32_t ph = 0;
+    struct Pair { int64_t seg, base, end; };
+    // segment ids are fetched ONE SEGMENT AHEAD: the atomic's round trip (~1 us) overlaps the pushes of the current segment
+    // instead of stalling the producer once per segment (short rows: as long as the segment's own HBM time)
+    auto issue_fetch = [&]() -> unsigned int { return lane == 0 ? atomicAdd(work_ctr, 1u) : 0u; };
+    auto take = [&](unsigned int v) -> int64_t { return static_cast<int64_t>(__shfl_sync(0xFFFFFFFFu, v, 0)); };
+    auto first_of = [&](int64_t seg) -> Pair {
+      Pair pr; pr.seg = seg;
+      if (seg >= n_seg) { pr.base = 0; pr.end = 0; return pr; }
+      const int64_t b = seg / splits;
+      const int64_t l0 = (seg - b * splits) * lc;
+      pr.base = l0; pr.end = min(L, l0 + lc);
+      return pr;
+    };
+    auto load_words = [&](const Pair& pr, int64_t (&m)[MR]) {
+#pragma unroll
+      for (int r = 0; r < MR; ++r) m[r] = 0;
+      if (pr.seg >= n_seg) return;
+      const int64_t* mb = mask + (pr.seg / splits) * L;
+      const int64_t stop = min(pr.end, pr.base + SB);
+#pragma unroll
+      for (int r = 0; r < MR; ++r) {
+        const int64_t l = pr.base + lane + 32 * r;
+        if (l < stop) m[r] = mb[l];
+      }
+    };
+    Pair nxt = first_of(take(issue_fetch()));
+    unsigned int ahead = issue_fetch();
+    int64_t nxt_m[MR];
+    load_words(nxt, nxt_m);
+    unsigned long long seg_wsum = 0;
     for (;;) {
-      unsigned int seg = 0;
-      if (lane == 0) seg = atomicAdd(work_ctr, 1u);
-      seg = __shfl_sync(0xFFFFFFFFu, seg, 0);
-      if (static_cast<int64_t>(seg) >= n_seg) {
+      const Pair cur = nxt;
+      int64_t m[MR];
+#pragma unroll
+      for (int r = 0; r < MR; ++r) m[r] = nxt_m[r];
+      if (cur.seg >= n_seg) {
         mbar_wait(&empty[s], ph ^ 1);
         if (lane == 0) { meta[s].seg = -1; meta[s].npos = 0; meta[s].last = 0; }
         __syncwarp();
         if (lane == 0) mbar_arrive(&full[s]);
         break;
       }
-      const int64_t b = seg / splits;
-      const int sp = static_cast<int>(seg - b * splits);
-      const int64_t l0 = sp * lc, l1 = min(L, l0 + lc);
-      const int64_t* mb = mask + b * L;
+      const bool last_sub = cur.base + SB >= cur.end;
+      if (last_sub) { nxt = first_of(take(ahead)); ahead = issue_fetch(); }
+      else { nxt = cur; nxt.base = cur.base + SB; }
+      load_words(nxt, nxt_m);   // in flight while the chunks of `cur` are pushed
+
+      const int64_t b = cur.seg / splits;
+      const int64_t stop = min(cur.end, cur.base + SB);
       unsigned long long wsum = 0;
       int lo = INT_MAX, hi = -1;
-      for (int64_t l = l0 + lane; l < l1; l += 32) {
-        const int64_t w = mb[l];
-        wsum += static_cast<unsigned long long>(w);
-        if (w != 0) { lo = min(lo, static_cast<int>(l - l0)); hi = max(hi, static_cast<int>(l - l0)); }
+#pragma unroll
+      for (int r = 0; r < MR; ++r) {
+        wsum += static_cast<unsigned long long>(m[r]);
+        if (m[r] != 0) { lo = min(lo, static_cast<int>(lane) + 32 * r); hi = max(hi, static_cast<int>(lane) + 32 * r); }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xFFFFFFFFu, wsum, o);
       lo = __reduce_min_sync(0xFFFFFFFFu, lo);
       hi = __reduce_max_sync(0xFFFFFFFFu, hi);
-      const int64_t n0 = (hi >= 0) ? l0 + lo : l0, n1 = (hi >= 0) ? l0 + hi + 1 : l0;   // empty when the whole segment is masked
+      seg_wsum += wsum;
       const unsigned char* hb = reinterpret_cast<const unsigned char*>(hidden + b * L * H);
-      int64_t p0 = n0;
-      do {
-        const int np = static_cast<int>(min(static_cast<int64_t>(CH), n1 - p0));
-        const bool last = p0 + np >= n1;
-        mbar_wait(&empty[s], ph ^ 1);
-        if (static_cast<int>(lane) < np) meta[s].w[lane] = static_cast<float>(mb[p0 + lane]);
-        if (lane == 0) { meta[s].seg = static_cast<int>(seg); meta[s].npos = np; meta[s].last = last ? 1 : 0; meta[s].wsum = wsum; }
-        __syncwarp();
-        if (lane == 0) {
-          if (np > 0) {
+      // chunks over the unmasked span of the sub-block, aligned to the chunk grid of the sub-block
+      if (hi >= 0) {
+        for (int c0 = (lo / CH) * CH; c0 <= hi; c0 += CH) {
+          const int first = max(c0, lo);
+          const int np = static_cast<int>(min(static_cast<int64_t>(min(c0 + CH, hi + 1)), stop - cur.base)) - first;
+          // weight of position first + lane: word (first + lane) of the sub-block lives in lane (idx % 32), register idx / 32
+          const int idx = first + static_cast<int>(lane);
+          float wv = 0.f;
+#pragma unroll
+          for (int r = 0; r < MR; ++r) {
+            const int64_t t = __shfl_sync(0xFFFFFFFFu, m[r], idx & 31);
+            if ((idx >> 5) == r) wv = static_cast<float>(t);
+          }
+          mbar_wait(&empty[s], ph ^ 1);
+          if (static_cast<int>(lane) < np) meta[s].w[lane] = wv;
+          if (lane == 0) { meta[s].seg = static_cast<int>(cur.seg); meta[s].npos = np; meta[s].last = 0; meta[s].wsum = 0ull; }
+          __syncwarp();
+          if (lane == 0) {
             const uint32_t bytes = static_cast<uint32_t>(np * row_bytes);
             mbar_expect_tx(&full[s], bytes);
-            bulk_load_1d(ring + s * stage_bytes, hb + p0 * row_bytes, bytes, &full[s]);
-          } else {
-            mbar_arrive(&full[s]);
+            bulk_load_1d(ring + s * stage_bytes, hb + (cur.base + first) * row_bytes, bytes, &full[s]);
           }
+          if (++s == stages) { s = 0; ph ^= 1; }
         }
+      }
+      if (last_sub) {
+        // the segment's terminator: no data, the mask sum of the whole segment
+        mbar_wait(&empty[s], ph ^ 1);
+        if (lane == 0) { meta[s].seg = static_cast<int>(cur.seg); meta[s].npos = 0; meta[s].last = 1; meta[s].wsum = seg_wsum; }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[s]);
         if (++s == stages) { s = 0; ph ^= 1; }
-        p0 += np;
-      } while (p0 < n1);
+        seg_wsum = 0;
+      }
     }
     // the last producer to leave puts the two scheduling words back to zero for the next launch on this workspace
     if (lane == 0) {
@@ -644,7 +698,15 @@ static int launch_pool_t(const void* hidden, const int64_t* mask, int64_t B, int
       const char* se = getenv("NXF_POOL_STREAM");
       const char* we = getenv("NXF_POOL_WS_CACHE");
       const bool ws_cached = we ? atoi(we) != 0 : NXF_POOL_WS_CACHE_DEFAULT != 0;
-      if (!(se && *se == '0') && ws_cached) {
+      // Measured (B200, same box, fraction of the HBM peak, stream | split): 3 000 x 128 x 384 f16 0.54 | 0.41, 1 024 x 256 x 1 024
+      // bf16 0.82 | -, 64 x 8 192 x 1 536 bf16 0.87 | 0.82, 256 x 512 x 768 f16 0.39 | 0.45.  The stream wins when a CTA owns whole
+      // rows (B >= 6 rows per SM: no cross-CTA combine) or rows are long (>= 1 MB: the per-segment combine is rare); in between the
+      // end-of-segment round trips (fence + arrival counter) on the consumers' path cost more than the split kernel's short CTAs.
+      // (A variant with dedicated finalizer warps was measured too: 0.25 / 0.52 / 0.67 -- slower; profiles/r2_k0_stream_variants.txt.)
+      const bool whole_rows = B >= 6 * 148;
+      const bool long_rows = L * H * static_cast<int64_t>(sizeof(T)) >= (int64_t(1) << 20);
+      const bool force = se && *se == '1';
+      if (!(se && *se == '0') && ws_cached && (whole_rows || long_rows || force)) {
         const int rc = launch_pool_mean_stream<T, O, VEC>(hidden, mask, B, L, H, normalize, eps, out, stream);
         if (rc <= 0) return rc;
       }
