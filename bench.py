@@ -614,7 +614,13 @@ def run_ours(a):
         if world == 1:
             small = small_batch_records(torch, idx, q, k, N, D, store, peaks)
             pool = pool_record(torch, peaks, device)
-        if world == 8 and a.config == "c2":
+        # NXF_BENCH_C3=Q,N forces the record at any rank count with a reduced shape (a dry run of this code path on 2 GPUs)
+        c3_env = os.environ.get("NXF_BENCH_C3", "")
+        if (world == 8 or c3_env) and world > 1 and a.config == "c2":
+            if c3_env:
+                cq, cn = (int(x) for x in c3_env.split(","))
+                _, _, cD, ck, cstore, cnorm, cdesc = CONFIGS["c3"]
+                CONFIGS["c3"] = (cq, cn, cD, ck, cstore, cnorm, cdesc + f" [reduced: {cq} x {cn}]")
             del idx, didx
             torch.cuda.empty_cache()
             c3 = run_c3(torch, dist, world, rank, local_rank, device, peaks, a.check_queries)

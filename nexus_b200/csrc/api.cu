@@ -550,6 +550,7 @@ struct SearchPlan {
   int level = 1;     // certified search: 1 candidate pass, 2 segmented retry, 3 exact kernels (no certificate needed)
   int cert = 0;      // evaluate the certificate in the arena merge
   float eps_rel = 0.f, eps_abs = 0.f;
+  int q_round = -1;  // type the candidate pass rounds the queries to (its share of the bound is measured per query), -1: none
   int seed = 0;      // K2T: threshold-seeding pass over the first tile of every CTA
   int cap = 0;
   int epi_sets = 2;
@@ -657,11 +658,13 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       // query rounding only: |q - q16| <= 2^-9 |q| -> every pass score within 2^-9 |q||c| of the fp32 score; k' = 2k keeps the gap
       // between ranks k and k' above that on the BASELINE configs (C2: 0.0069 against 0.0020)
       kf = std::max<int64_t>(static_cast<int64_t>(std::max(1, env_int("NXF_KFETCH_MULT16", 2))) * P.k_eff, P.k_eff + 16);
-      P.eps_rel = 0.001953125f + acc_slack(kb);
+      P.q_round = idx->store_dtype;          // the merge measures |q - round(q)| itself (<= 2^-9 |q|, ~0.6 of that on average)
+      P.eps_rel = acc_slack(kb);
     } else {
       // fp32 rows through their bf16 hi plane: both operands rounded, (2^-8 + 2^-16) |q||c|; k' = 4k
       kf = std::max<int64_t>(static_cast<int64_t>(std::max(1, env_int("NXF_KFETCH_MULT32", 4))) * P.k_eff, P.k_eff + 64);
-      P.eps_rel = 0.00390625f + 1.52587890625e-05f + acc_slack(kb);
+      P.q_round = NXF_BF16;                  // query part measured; the rows' part: |round(q) . (c - bf16(c))| <= (1 + 2^-9) |q| 2^-9 |c|
+      P.eps_rel = 0.001953125f * 1.002f + acc_slack(kb);
     }
     if (idx->store_dtype == NXF_F16) P.eps_abs = std::sqrt(static_cast<float>(idx->dim)) * 5.9604644775390625e-08f;  // f16 subnormals: 2^-24 per element
     kf = (kf + 7) / 8 * 8;
@@ -1094,7 +1097,7 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
     mp.arena = arena; mp.qcnt = qcnt; mp.arena_stride = arena_stride; mp.k_fetch = P.k_fetch; mp.k_out = k; mp.metric = idx->metric;
     mp.rescore = P.rescore; mp.q = q_f32; mp.ldq = idx->ld; mp.corpus = idx->data; mp.ld = idx->ld; mp.dim = idx->dim;
     mp.id_offset = idx->id_offset;
-    mp.cert = P.cert; mp.eps_rel = P.eps_rel; mp.eps_abs = P.eps_abs; mp.max_norm2 = idx->max_norm2; mp.n_rows = idx->n;
+    mp.cert = P.cert; mp.q_round = P.q_round; mp.eps_rel = P.eps_rel; mp.eps_abs = P.eps_abs; mp.max_norm2 = idx->max_norm2; mp.n_rows = idx->n;
     mp.cert_fail = P.cert ? cert_w + b0 : nullptr; mp.cert_count = P.cert ? cert_w + nq : nullptr;
     mp.out_scores = out_on_device ? (out_scores ? out_scores + b0 * k : nullptr) : o_scores;
     mp.out_ids = out_on_device ? (out_ids ? out_ids + b0 * k : nullptr) : o_ids;

@@ -34,8 +34,8 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
   __shared__ uint32_t hist[256];
   __shared__ uint32_t sh_prefix;
   __shared__ int sh_need, sh_gt, sh_eq, sh_live;
-  __shared__ float sh_qnorm, sh_tau_min, sh_sk;
-  __shared__ float red[mg::THREADS / 32];
+  __shared__ float sh_qnorm, sh_qlo, sh_tau_min, sh_sk;
+  __shared__ float red[mg::THREADS / 32], red_lo[mg::THREADS / 32];
 
   const int64_t qi = blockIdx.x;
   const int tid = threadIdx.x;
@@ -48,20 +48,25 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
 
   const bool need_q = p.rescore || p.metric == NXF_METRIC_L2;
   if (need_q) {
-    float part = 0.f;
+    float part = 0.f, part_lo = 0.f;
     for (int d = tid; d < static_cast<int>(p.ld); d += mg::THREADS) {  // ldq >= ld and both are zero padded past dim
       const float v = d < p.dim ? p.q[qi * p.ldq + d] : 0.f;
       q_s[d] = v;
       part += v * v;
+      if (p.cert && p.q_round >= 0) {   // what the candidate pass lost of this query: q - round(q)
+        const float r = p.q_round == NXF_F16 ? __half2float(__float2half_rn(v)) : __bfloat162float(__float2bfloat16_rn(v));
+        part_lo = fmaf(v - r, v - r, part_lo);
+      }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(kFullMask, part, o);
-    if ((tid & 31) == 0) red[tid >> 5] = part;
+    for (int o = 16; o > 0; o >>= 1) { part += __shfl_xor_sync(kFullMask, part, o); part_lo += __shfl_xor_sync(kFullMask, part_lo, o); }
+    if ((tid & 31) == 0) { red[tid >> 5] = part; red_lo[tid >> 5] = part_lo; }
     __syncthreads();
     if (tid == 0) {
-      float s = 0.f;
-      for (int w = 0; w < mg::THREADS / 32; ++w) s += red[w];
+      float s = 0.f, sl = 0.f;
+      for (int w = 0; w < mg::THREADS / 32; ++w) { s += red[w]; sl += red_lo[w]; }
       sh_qnorm = s;
+      sh_qlo = sl;
     }
   }
   const bool staged = M <= mg::STAGE;
@@ -105,7 +110,7 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
       for (int w = 1; w < mg::THREADS / 32; ++w) m = fminf(m, red[w]);
       sh_tau_min = m;
     }
-    eps = (p.eps_rel * sqrtf(sh_qnorm) + p.eps_abs) * sqrtf(__uint_as_float(*p.max_norm2)) * 1.0001f;
+    eps = (sqrtf(sh_qlo) * 1.001f + p.eps_rel * sqrtf(sh_qnorm) + p.eps_abs) * sqrtf(__uint_as_float(*p.max_norm2)) * 1.0001f;
   }
 
   // ---- the candidates worth re-scoring -> live[0, n_live) ----

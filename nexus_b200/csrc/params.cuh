@@ -133,7 +133,9 @@ struct MergeArenaParams {
   // smallest kept pass score), hence a true score <= tau' + eps with eps = eps_rel * |q| * max|c| (+ eps_abs * max|c|); the re-scored
   // top-k is exact iff its k-th true score >= tau' + eps.  Queries that fail are flagged for the retry level.
   int cert;                   // evaluate it (needs rescore)
-  float eps_rel, eps_abs;
+  int q_round;                // the pass saw the queries rounded to this type (NXF_BF16 / NXF_F16; -1: exactly, e.g. as [hi | mid] planes):
+                              // that part of the bound is the ACTUAL |q - round(q)| of the query, not the worst case 2^-9 |q|
+  float eps_rel, eps_abs;     // everything else, relative to |q| (row rounding of fp32 storage, accumulation slack) / absolute
   const uint32_t* max_norm2;  // device word: float bits of max over stored rows of |row|^2
   int64_t n_rows;             // rows in the index (a query that kept them all passes)
   uint32_t* cert_fail;        // [nq] 1 = failed
