@@ -1315,7 +1315,17 @@ int nxf_search_subsets(nxf_index* idx, const void* q, int64_t nq, int q_dtype, i
     NXF_CUDA(cudaEventCreate(&pe1));
     NXF_CUDA(cudaEventRecord(pe0, stream));
   }
-  rc = launch_subset_search(idx->store_dtype, sp, nq, stream);
+  int64_t min_len = -1, max_len = -1;   // known for host lists: lets the launcher skip the kernel (CTA / warp per list) nobody needs
+  if (!lists_on_device) {
+    min_len = INT64_MAX; max_len = 0;
+    for (int64_t i = 0; i < nq; ++i) {
+      const int64_t len = offsets[i + 1] - offsets[i];
+      min_len = std::min(min_len, len); max_len = std::max(max_len, len);
+    }
+    if (min_len < 0) { min_len = -1; max_len = -1; }   // malformed: both kernels run and report it
+  }
+  sp.short_max = -1;
+  rc = launch_subset_search(idx->store_dtype, sp, nq, min_len, max_len, stream);
   if (rc) return rc;
   idx->stats.kernel_launches++;
   if (pe0) {

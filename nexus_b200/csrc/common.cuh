@@ -37,6 +37,26 @@ int ensure_dyn_smem(const void* kernel, int bytes);
     }                                   \
   } while (0)
 
+// Device-side bounds checks of the "cannot happen by construction" kind (private candidate buffers, arena slices, ring slots).
+// compute-sanitizer is not available on the GPU pool this was developed on, so a CHECKED build (-DNXF_CHECKED=1,
+// tools/build_variant.sh checked "-DNXF_CHECKED=1") traps with a message at the first violated bound instead; the test-suite and
+// tools/sanitize_cases.py are run against it (NEXUS_FLAT_LIB=...) and the log is kept under profiles/.  Compiled out otherwise.
+#ifndef NXF_CHECKED
+#define NXF_CHECKED 0
+#endif
+#if NXF_CHECKED
+#define NXF_DEV_CHECK(cond, what)                                                                                     \
+  do {                                                                                                                \
+    if (!(cond)) {                                                                                                    \
+      printf("[nxf checked build] %s:%d: bound violated: %s (block %d thread %d)\n", __FILE__, __LINE__, what,       \
+             static_cast<int>(blockIdx.x), static_cast<int>(threadIdx.x));                                            \
+      __trap();                                                                                                       \
+    }                                                                                                                 \
+  } while (0)
+#else
+#define NXF_DEV_CHECK(cond, what) do { } while (0)
+#endif
+
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int64_t round_up64(int64_t a, int64_t b) { return ceil_div64(a, b) * b; }
 

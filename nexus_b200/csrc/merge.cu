@@ -41,9 +41,11 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
   const int tid = threadIdx.x;
   const Entry* __restrict__ gsrc = p.arena + qi * p.arena_stride;
   int64_t m64 = p.qcnt[qi];
+  NXF_DEV_CHECK(m64 <= p.arena_stride, "arena slice count beyond its stride");
   if (m64 > p.arena_stride) m64 = p.arena_stride;
   const int M = static_cast<int>(m64);
   const int keep = min(M, p.k_fetch);
+  NXF_DEV_CHECK(keep <= mg::MAXK, "k' beyond the merge's shared-memory arrays");
   Entry* ent = reinterpret_cast<Entry*>(keys);  // gather target aliases the key array (8 B each)
 
   const bool need_q = p.rescore || p.metric == NXF_METRIC_L2;
@@ -121,7 +123,11 @@ __global__ void __launch_bounds__(mg::THREADS) merge_arena_kernel(MergeArenaPara
     const float floor_s = okey_inv(sh_prefix) - 2.f * eps;     // a_k - 2 eps
     for (int i = tid; i < keep; i += mg::THREADS) {
       const Entry e = ent[i];
-      if (e.score >= floor_s) stage[atomicAdd(&sh_live, 1)] = e;
+      if (e.score >= floor_s) {
+        const int at = atomicAdd(&sh_live, 1);
+        NXF_DEV_CHECK(at < mg::STAGE, "live candidate list overflow");
+        stage[at] = e;
+      }
     }
     __syncthreads();
     live = stage;

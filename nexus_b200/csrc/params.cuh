@@ -167,6 +167,7 @@ struct SubsetParams {
   float* out_scores;       // [nq, k_out]
   int64_t* out_pos;        // [nq, k_out] positions inside the query's own list, -1 = padding
   uint32_t* err;           // bit 0: a row id outside [0, n_rows); bit 1: malformed offsets
+  int short_max;           // lists of up to this many entries are served by the warp-per-list kernel (-1: none)
 };
 
 constexpr int kMaxPackedLists = 64;
@@ -202,7 +203,7 @@ int launch_select_tau(Entry* arena, uint32_t* qcnt, int64_t arena_stride, int m,
 int launch_verify_counts(uint32_t* qcnt, uint32_t* tau_g, int64_t nq, int need, uint32_t* flag, cudaStream_t stream);
 int launch_merge_arena(int store_dtype, const MergeArenaParams& p, int64_t nq, cudaStream_t stream);
 int launch_merge_lists(const MergeListsParams& p, cudaStream_t stream);
-int launch_subset_search(int store_dtype, const SubsetParams& p, int64_t nq, cudaStream_t stream);
+int launch_subset_search(int store_dtype, const SubsetParams& p, int64_t nq, int64_t min_len, int64_t max_len, cudaStream_t stream);
 int launch_positive_rank(const float* pos, const float* topk, int64_t nq, int k, int32_t* rank, uint8_t* pred, cudaStream_t stream);
 int launch_convert_rows(const void* src, int src_dtype, int64_t src_ld, void* dst, int dst_dtype, int64_t dst_ld, int64_t n, int dim,
                         cudaStream_t stream);

@@ -474,6 +474,7 @@ __global__ void __launch_bounds__(k0s::THREADS, 1) pool_mean_stream_kernel(const
             if ((idx >> 5) == r) wv = static_cast<float>(t);
           }
           mbar_wait(&empty[s], ph ^ 1);
+          NXF_DEV_CHECK(np >= 1 && np <= CH && cur.base + first + np <= cur.end, "K0 chunk outside its segment");
           if (static_cast<int>(lane) < np) meta[s].w[lane] = wv;
           if (lane == 0) { meta[s].seg = static_cast<int>(cur.seg); meta[s].npos = np; meta[s].last = 0; meta[s].wsum = 0ull; }
           __syncwarp();

@@ -213,6 +213,7 @@ __global__ void __launch_bounds__(k2::THREADS, 1) k2_stream_kernel(K2Params p) {
           Entry* buf = my_cand + static_cast<int64_t>(qi) * cap;
           if (mine) {
             Entry e; e.score = sc; e.row = static_cast<int32_t>(grow);
+            NXF_DEV_CHECK(cnt[qi] + __popc(m) <= cap, "K2 per-(warp, query) buffer overflow");
             buf[cnt[qi] + __popc(m & lanemask_lt())] = e;
           }
           cnt[qi] += __popc(m);

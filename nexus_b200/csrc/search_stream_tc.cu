@@ -100,6 +100,7 @@ __device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], const TauSli
       if (d[j] > 0.f) {  // v > tau (tau = +inf for padded columns gives d = -inf / NaN: never true)
         const int qi = ch * 16 + j;
         const int pos = atomicAdd(&cnt_s[qi], 1);
+        NXF_DEV_CHECK(pos < cap, "K2T per-(CTA, query) list overflow");
         const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
         cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(v[j]);
         cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);

@@ -147,6 +147,8 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&vr)[32], int32_t cbas
     st.cnt = static_cast<int>(w - my_first);
   }
 }
+// (the bound of these thread-private appends -- a row gains <= 256 entries per tile and is pruned once fewer than 256 slots are
+// left -- is asserted after every tile in the kernel: NXF_DEV_CHECK(cur.cnt <= cap))
 
 // Round schedule shared by the three warp roles.  Line positions [a, b) of cluster j in a round of R tiles cover
 // query tiles qt = pos / R at corpus offsets pos % R.
@@ -390,6 +392,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               else epi_chunk<false>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
             }
           }
+          NXF_DEV_CHECK(cur.cnt <= cap, "K1 private candidate buffer overflow");
           // other owners' progress on this query: loaded during the previous tile, folded in only now so that its latency
           // hides behind phase A
           cur.tau = fmaxf(cur.tau, tau_next);
@@ -445,6 +448,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // one atomic per row, all 32 in flight together; then the warp copies the rows one after the other
       uint32_t my_pos = 0;
       if (my_cnt > 0) my_pos = atomicAdd(&p.sink.qcnt[my_q], static_cast<uint32_t>(my_cnt));
+      NXF_DEV_CHECK(static_cast<int64_t>(my_pos) + my_cnt <= p.sink.arena_stride, "K1 arena slice overflow");
       if (static_cast<int64_t>(my_pos) + my_cnt > p.sink.arena_stride) my_cnt = 0;  // cannot happen by construction; never write OOB
       unsigned todo = __ballot_sync(kFullMask, my_cnt > 0);
       while (todo) {

@@ -31,6 +31,7 @@ __device__ __forceinline__ void warp_flush(const SinkParams& sp, const Entry* __
   if (lane_id() == 0) pos = atomicAdd(&sp.qcnt[query], static_cast<uint32_t>(n));
   pos = __shfl_sync(kFullMask, pos, 0);
   Entry* dst = sp.arena + query * sp.arena_stride + pos;
+  NXF_DEV_CHECK(static_cast<int64_t>(pos) + n <= sp.arena_stride, "arena slice overflow in warp_flush");
   if (static_cast<int64_t>(pos) + n > sp.arena_stride) return;  // cannot happen by construction; never write OOB
   for (int i = lane_id(); i < n; i += 32) dst[i] = buf[i];
 }
