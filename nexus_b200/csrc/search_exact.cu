@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(kx::THREADS) kx_search_kernel(KxParams p) {
           if (gr < p.n && s > tau) {
             const int pos = atomicAdd(&cnt_s[row], 1);
             Entry e; e.score = s; e.row = static_cast<int32_t>(gr);
+            NXF_DEV_CHECK(pos < cap, "KX per-row candidate buffer overflow");
             my_cand[static_cast<int64_t>(row) * cap + pos] = e;
           }
         }
