@@ -80,7 +80,13 @@ def main():
     # ---- certificate failures: the segmented retry level and the exact kernels ----
     from test_gpu_certified import _near_duplicates
     for store in ("f32", "bf16"):
-        cc, xx = _near_duplicates(4000, 600, 64, 130, 2e-5, seed=1)
+        if store == "f32":
+            cc, xx = _near_duplicates(4000, 600, 64, 130, 2e-5, seed=1)
+        else:   # 16-bit storage spreads near-copies apart when it rounds them: bit-identical copies instead
+            bg, xx = unit(4000, 64), unit(130, 64)
+            best = oracle.round_to_bf16(0.9 * xx + 0.01 * rng.standard_normal(xx.shape).astype(np.float32))
+            cc = np.concatenate([bg, np.repeat(best, 300, axis=0)], axis=0)
+            cc = np.ascontiguousarray(cc[rng.permutation(cc.shape[0])])
         idx = FlatIndex(64, "ip", store)
         idx.add(cc)
         D, I = idx.search(xx, 50)

@@ -57,8 +57,10 @@ def main():
         idx.set_profiling(False)
         kms = st["main_kernel_ms"] / max(1, st["main_kernel_count"])
         total = e0.elapsed_time(e1) / a.iters
-        gbs = N * ld * esz / (kms * 1e-3) / 1e9
-        print(json.dumps({"config": a.config, "n": N, "dim": D, "store": store, "k": k, "nq": nq, "path": st["last_path_name"], "kernel_ms": round(kms, 4),
+        # bytes the kernel streams per element: the tensor paths read 16-bit rows (fp32 storage: its bf16 plane), K2 / KX the rows as stored
+        esz_k = 2 if (store != "f32" or st["last_path_name"] in ("tstream", "tensor")) else 4
+        gbs = N * ld * esz_k / (kms * 1e-3) / 1e9
+        print(json.dumps({"config": a.config, "n": N, "dim": D, "store": store, "k": k, "nq": nq, "path": st["last_path_name"], "streamed_bytes_per_element": esz_k, "kernel_ms": round(kms, 4),
                           "call_ms": round(total, 4), "GBps": round(gbs, 1), "frac_of_measured_hbm": round(gbs / peaks["hbm_gbs"], 3),
                           "qps": round(nq / (total * 1e-3), 1), "grid": st["last_grid"], "chunks": st["last_chunks"]}), flush=True)
 
