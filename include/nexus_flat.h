@@ -252,6 +252,19 @@ NXF_API int nxf_pool_normalize(const void* hidden, int h_dtype, const int64_t* m
                                int64_t H, int pooling, int normalize, float eps, void* out, int out_dtype,
                                int device, void* stream);
 
+/* ---- mean pooling without any allocation (device pointers only) ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * nxf_pool_normalize(..., NXF_POOL_MEAN, ...), but the kernel's workspace (per-row control words + fp32 partial sums) is a static
+ * __device__ array inside the library instead of a cached cudaMalloc'd buffer: the call allocates and frees NOTHING (no cudaMalloc,
+ * cudaFree, stream-ordered or library allocation).  Every GPU that loads the library holds that array (64 KB + 8 MB) until exit.
+ * Limits, rejected with NXF_EINVAL / NXF_EUNSUPPORTED and a message: B <= 4096 rows; B * H * 4 bytes <= 8 MB; hidden states
+ * 16-byte aligned with H * sizeof(element) a multiple of 16 and at most 512 such vectors per row; mask must not be NULL.
+ * All calls share the one array per device and it keeps the last call's contents (the control words are cleared on `stream`
+ * before every launch): calls that may overlap on the GPU -- two streams, two threads -- race; order them yourself. */
+NXF_API int nxf_pool_mean_normalize_static(const void* hidden, int h_dtype, const int64_t* mask, int64_t B, int64_t L, int64_t H,
+                                           int normalize, float eps, void* out, int out_dtype, int device, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

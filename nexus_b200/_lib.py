@@ -35,7 +35,7 @@ EXPORTS = [
     "nxf_ntotal", "nxf_dim", "nxf_metric", "nxf_store_dtype", "nxf_device", "nxf_set_id_offset", "nxf_get_stats",
     "nxf_set_profiling",
     "nxf_add", "nxf_reconstruct", "nxf_search", "nxf_search_subsets", "nxf_merge_topk", "nxf_positive_rank", "nxf_pool_normalize",
-    "nxf_search_packed", "nxf_merge_packed",
+    "nxf_search_packed", "nxf_merge_packed", "nxf_pool_mean_normalize_static",
 ]
 
 
@@ -99,6 +99,7 @@ def load() -> C.CDLL:
         lib.nxf_merge_packed.argtypes = [vp, C.POINTER(i64), i32, i64, i32, i32, i32, vp, vp, i32, vp]
         lib.nxf_positive_rank.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp]
         lib.nxf_pool_normalize.argtypes = [vp, i32, vp, i64, i64, i64, i32, i32, C.c_float, vp, i32, i32, vp]
+        lib.nxf_pool_mean_normalize_static.argtypes = [vp, i32, vp, i64, i64, i64, i32, C.c_float, vp, i32, i32, vp]
         for name in EXPORTS:
             fn = getattr(lib, name)  # raises AttributeError if the symbol is not exported
             if name not in ("nxf_version", "nxf_last_error", "nxf_destroy", "nxf_ntotal"):

@@ -760,4 +760,113 @@ int launch_pool(const void* hidden, int h_dtype, const int64_t* mask, int64_t B,
   return NXF_EINVAL;
 }
 
+// ---- mean pooling without any allocation: nxf_pool_mean_normalize_static ---------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the split
+// mean kernel above with its workspace (per-row control words + fp32 partial sums) in a file-scope __device__ array instead of the
+// cached cudaMalloc'd workspace.  Every GPU that loads the library holds the array (kStaticScratchBytes = 64 KB + 8 MB) until the
+// process exits.  In HOST code the array's name is a host-side stand-in, not a device address: the address the kernel gets comes
+// from cudaGetSymbolAddress, taken once per device with that device current.  All calls share the array and it keeps the last
+// call's contents: the control words are cleared on the call's stream before every launch; calls that overlap on the GPU race.
+constexpr size_t kStaticCtlBytes = 64 * 1024;               // den (u64) + arrival counter (u32) for up to kStaticMaxRows rows
+constexpr size_t kStaticPartBytes = size_t(8) << 20;        // fp32 partial sums [B][splits][H]
+constexpr size_t kStaticScratchBytes = kStaticCtlBytes + kStaticPartBytes;
+constexpr int64_t kStaticMaxRows = 4096;                    // 4096 * 8 + 4096 * 4 = 48 KB of control words
+static __device__ __align__(256) unsigned char g_pool_static_scratch[kStaticScratchBytes];
+
+namespace {
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[64] = {nullptr};   // device address of the array, per device ordinal
+
+// the device must be current
+int static_scratch_address(int device, unsigned char** out) {
+  if (device < 0 || device >= 64) { set_error("nxf_pool_mean_normalize_static: device ordinal %d outside [0, 64)", device); return NXF_EINVAL; }
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (g_static_ptr[device] == nullptr) {
+    void* ptr = nullptr;
+    NXF_CUDA(cudaGetSymbolAddress(&ptr, g_pool_static_scratch));
+    g_static_ptr[device] = static_cast<unsigned char*>(ptr);
+  }
+  *out = g_static_ptr[device];
+  return NXF_OK;
+}
+
+template <typename T, typename O, int VEC>
+int launch_pool_mean_static_t(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int normalize, float eps, void* out,
+                              unsigned char* scratch, cudaStream_t stream) {
+  const int nvec = static_cast<int>(H / VEC);
+  if (nvec > 512 || static_cast<size_t>(std::max(1, 512 / nvec)) * H * 4 > 160 * 1024) {
+    set_error("nxf_pool_mean_normalize_static: hidden size %lld does not fit the split kernel (at most 512 16-byte vectors per row)", (long long)H);
+    return NXF_EUNSUPPORTED;
+  }
+  const int G = std::max(1, 512 / nvec);
+  const int threads = std::min(512, (G * nvec + 31) / 32 * 32);
+  // as many slices of L per row as the split kernel would take, halved until the partial sums fit the static array
+  int splits = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>((NXF_POOL_CTAS + B - 1) / B, std::max<int64_t>(1, L / 64))));
+  while (splits > 1 && static_cast<size_t>(B) * splits * H * 4 > kStaticPartBytes) splits = (splits + 1) / 2;
+  if (static_cast<size_t>(B) * splits * H * 4 > kStaticPartBytes) {
+    set_error("nxf_pool_mean_normalize_static: B * H * 4 = %lld bytes of partial sums exceed the static scratch (%lld bytes)",
+              (long long)(B * H * 4), (long long)kStaticPartBytes);
+    return NXF_EINVAL;
+  }
+  const size_t smem = static_cast<size_t>(G) * H * 4;
+  auto kern = pool_mean_split_kernel<T, O, VEC>;
+  if (smem > 48 * 1024) { if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), static_cast<int>(smem))) return rc; }
+  unsigned long long* den = reinterpret_cast<unsigned long long*>(scratch);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(scratch + kStaticMaxRows * 8);
+  float* partial = reinterpret_cast<float*>(scratch + kStaticCtlBytes);
+  // whatever an earlier (possibly aborted) call left behind: the control words must start at zero
+  NXF_CUDA(cudaMemsetAsync(scratch, 0, static_cast<size_t>(kStaticMaxRows) * 12, stream));
+  kern<<<dim3(static_cast<unsigned>(splits), static_cast<unsigned>(B)), threads, smem, stream>>>(
+      (const T*)hidden, mask, L, H, normalize, eps, (O*)out, G, partial, den, counter);
+  NXF_CUDA(cudaGetLastError());
+  return NXF_OK;
+}
+
+template <typename T, int VEC>
+int launch_pool_mean_static_o(const void* hidden, const int64_t* mask, int64_t B, int64_t L, int64_t H, int normalize, float eps, void* out,
+                              int out_dtype, unsigned char* scratch, cudaStream_t stream) {
+  switch (out_dtype) {
+    case NXF_F32: return launch_pool_mean_static_t<T, float, VEC>(hidden, mask, B, L, H, normalize, eps, out, scratch, stream);
+    case NXF_F16: return launch_pool_mean_static_t<T, __half, VEC>(hidden, mask, B, L, H, normalize, eps, out, scratch, stream);
+    case NXF_BF16: return launch_pool_mean_static_t<T, __nv_bfloat16, VEC>(hidden, mask, B, L, H, normalize, eps, out, scratch, stream);
+  }
+  set_error("nxf_pool_mean_normalize_static: bad output dtype %d", out_dtype);
+  return NXF_EINVAL;
+}
+}  // namespace
+
 }  // namespace nxf
+
+// C ABI (declared in include/nexus_flat.h).  Defined here, not in api.cu: only this translation unit can name the static array.
+extern "C" int nxf_pool_mean_normalize_static(const void* hidden, int h_dtype, const int64_t* mask, int64_t B, int64_t L, int64_t H,
+                                              int normalize, float eps, void* out, int out_dtype, int device, void* stream_) {
+  using namespace nxf;
+  NXF_REQUIRE(hidden != nullptr && out != nullptr && mask != nullptr, "nxf_pool_mean_normalize_static: NULL buffer");
+  NXF_REQUIRE(B >= 0 && L >= 1 && H >= 1, "nxf_pool_mean_normalize_static: bad shape B=%lld L=%lld H=%lld", (long long)B, (long long)L, (long long)H);
+  NXF_REQUIRE(B <= kStaticMaxRows, "nxf_pool_mean_normalize_static: B=%lld rows exceed the static scratch's maximum of %lld (use nxf_pool_normalize)",
+              (long long)B, (long long)kStaticMaxRows);
+  if (B == 0) return NXF_OK;
+  const bool aligned = reinterpret_cast<uintptr_t>(hidden) % 16 == 0;
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice", __FILE__, __LINE__);
+  unsigned char* scratch = nullptr;
+  int rc = static_scratch_address(device, &scratch);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (rc == NXF_OK) {
+    if (h_dtype == NXF_F32 && aligned && H % 4 == 0)
+      rc = launch_pool_mean_static_o<float, 4>(hidden, mask, B, L, H, normalize, eps, out, out_dtype, scratch, stream);
+    else if (h_dtype == NXF_F16 && aligned && H % 8 == 0)
+      rc = launch_pool_mean_static_o<__half, 8>(hidden, mask, B, L, H, normalize, eps, out, out_dtype, scratch, stream);
+    else if (h_dtype == NXF_BF16 && aligned && H % 8 == 0)
+      rc = launch_pool_mean_static_o<__nv_bfloat16, 8>(hidden, mask, B, L, H, normalize, eps, out, out_dtype, scratch, stream);
+    else {
+      set_error("nxf_pool_mean_normalize_static: needs f32/f16/bf16 hidden states, 16-byte aligned, H a multiple of 16 bytes (dtype %d, H %lld)",
+                h_dtype, (long long)H);
+      rc = NXF_EUNSUPPORTED;
+    }
+  }
+  if (prev >= 0 && prev != device) cudaSetDevice(prev);
+  return rc;
+}
