@@ -671,7 +671,10 @@ def run_ours(a):
         "data": "synthetic",
         "config": make_config(a, world),
         "plan": {"path": path, "k_fetch": st1["last_k_fetch"], "chunks": st1["last_chunks"], "grid": st1["last_grid"], "index_build_s": t_build,
-                 "exchange": ("partition" if partitioned else "gather") if world > 1 else None, "host_threads": host_threads_in_use()},
+                 "exchange": ("partition" if partitioned else "gather") if world > 1 else None, "host_threads": host_threads_in_use(),
+                 # certified search over the timed steps (rank 0's shard): queries checked / searched again by the segmented pass / by the exact kernels
+                 "certificate": {"checked": st1["cert_checked"] - st0["cert_checked"], "retry_segmented": st1["cert_retry_l2"] - st0["cert_retry_l2"],
+                                 "retry_exact": st1["cert_retry_l3"] - st0["cert_retry_l3"]}},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "check": check,
     }
     if small is not None:
