@@ -575,7 +575,19 @@ constexpr int kForceMask = NXF_SEARCH_FORCE_EXACT | NXF_SEARCH_FORCE_STREAM | NX
 // fp32 accumulation of the tensor cores over `kblocks` K blocks of 64 elements: 4 MMAs per block, two roundings each (the sum of
 // the 16 products, then the add into the accumulator), each taken as <= 1 ulp (2^-23, doubled for a truncating adder) of a
 // partial sum that never exceeds sum|q_i c_i| <= |q||c|
-float acc_slack(int kblocks) { return static_cast<float>(kblocks * 8 + 16) * 2.384185791015625e-07f; }
+// (+8 of the constant: K2T's threshold fold -- one more MMA, the 2^-24-relative residual of the three-piece threshold and the
+// d + tau reconstruction of a survivor's score)
+float acc_slack(int kblocks) { return static_cast<float>(kblocks * 8 + 24) * 2.384185791015625e-07f; }
+
+// K2T's threshold fold (search_stream_tc.cu), an experiment kept behind NXF_K2T_FOLD=1: short rows, many queries.  Measured on the C5
+// corpus (profiles/r2_k2t_knockout.md): 128 queries k = 10, main launch 298 -> 282 us, but +9 us on the sample launch and 368 -> 453 us at
+// k = 500 (every survivor re-reads its 32-query block); 64 queries and fewer: slower.  Not the default.
+bool k2t_use_fold(const nxf_index* idx, int nq_pad) {
+  if (env_int("NXF_K2T_FOLD", 0) == 0) return false;
+  if (idx->metric != NXF_METRIC_IP) return false;
+  if (idx->store_dtype != NXF_BF16 && idx->store_dtype != NXF_F32) return false;   // fp32 rows: K2T streams their bf16 plane
+  return idx->ld / 64 <= env_int("NXF_K2T_FOLD_MAX_KB", 2) && nq_pad >= env_int("NXF_K2T_FOLD_MIN_NQ", 32);
+}
 
 }  // namespace
 
@@ -603,8 +615,10 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
   if (path == NXF_PATH_TSTREAM) {
     // K2T keeps the (16-padded) queries resident in shared memory; if that leaves fewer than 4 ring stages fall back to the kernels
     // that do not need it
-    const int nq_pad = static_cast<int>(round_up64(std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ), 16));
-    const int st = tens ? k2t_plan_stages(static_cast<int>(idx->ld / 64), nq_pad) : 0;
+    int nq_pad = static_cast<int>(round_up64(std::min<int64_t>(nq, NXF_TSTREAM_MAX_NQ), 16));
+    const bool fold = k2t_use_fold(idx, nq_pad);
+    if (fold) nq_pad = (nq_pad + 31) & ~31;   // the folded filter reads the accumulator 32 columns at a time
+    const int st = tens ? k2t_plan_stages(static_cast<int>(idx->ld / 64), nq_pad, fold) : 0;
     if (st == 0) {
       if (flags & NXF_SEARCH_FORCE_TSTREAM) {
         set_error("nxf_search: the tensor stream kernel needs queries that fit in shared memory (nq=%lld, dim=%d) and, for f32 storage, the bf16 plane",
@@ -922,12 +936,23 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
     } else if (P.path == NXF_PATH_TSTREAM) {
       K2TParams kp;
       kp.n = idx->n; kp.nq = static_cast<int>(bn); kp.nq_pad = static_cast<int>(round_up64(bn, 16)); kp.kblocks = static_cast<int>(idx->ld / 64);
-      kp.stages = k2t_plan_stages(kp.kblocks, kp.nq_pad);
+      // bf16 rows (or the bf16 plane of fp32 rows), ip, short rows, many queries: the threshold comparison moves into the tensor core
+      // (and a round of at least 2 * tbufs tiles: the issuer must never be two threshold versions ahead of the epilogue)
+      kp.fold = (k2t_use_fold(idx, kp.nq_pad) && c_dt == NXF_BF16 && P.epi_sets * P.rw >= 16) ? 1 : 0;
+      if (kp.fold) kp.nq_pad = (kp.nq_pad + 31) & ~31;   // 32-column accumulator loads (P.nq_t was planned the same way)
+      kp.q_f32 = q_f32; kp.ldq = idx->ld; kp.dim = idx->dim; kp.max_norm2 = idx->max_norm2;
+      kp.stages = k2t_plan_stages(kp.kblocks, kp.nq_pad, kp.fold);
+      // (an even number of sets: a set then only ever sees tiles of one issuer, which complete in order -- its parity wait on an
+      // accumulator buffer would otherwise be able to run a whole phase ahead of the other issuer)
+      kp.issuers = (kp.stages >= 2 * kp.kblocks && P.epi_sets % 2 == 0 && env_int("NXF_K2T_ISSUERS", 1) == 2) ? 2 : 1;
       kp.tbuf_stride = kp.nq_pad <= 32 ? 32 : (kp.nq_pad <= 64 ? 64 : 128);
       kp.tbufs = std::min(8, 512 / kp.tbuf_stride);
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.check_every = P.rw;
       kp.epi_sets = P.epi_sets;
+      // NXF_K2T_CS=2 (experiment, no gain measured: 297.7 vs 297.7 us at 128 queries): pairs of sets share a tile, half the slices each
+      kp.col_split = (P.epi_sets % 2 == 0 && kp.nq_pad >= 32 && env_int("NXF_K2T_CS", 1) == 2) ? 2 : 1;
+      if (kp.fold) kp.col_split = 1;   // the folded filter takes whole rows
       kp.sink = sink;
       kp.sink.cap = P.cap;
       const int64_t c_ld = idx->ld;

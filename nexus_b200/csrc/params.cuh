@@ -107,6 +107,8 @@ struct K2TParams {
   int tbuf_stride;  // TMEM columns between buffers
   int check_every;  // tiles per epilogue set between two buffer-overflow checks (cap = 2k' + epi_sets*128*check_every)
   int epi_sets;     // 2..4 epilogue warp sets (four warps each, one per SM sub-partition); set s filters tiles s, s + epi_sets, ...
+  int issuers;      // 1, or 2 (stages >= 2 * kblocks): two warps issue the MMAs of alternate tiles
+  int col_split;    // 1, or 2 (epi_sets even): pairs of sets share a tile, each filtering half of the query slices
   // a search is 1-3 launches over consecutive tile ranges (DESIGN.md "K2T, threshold seeding"); the per-(CTA, query) lists and
   // their counts stay in global memory between launches
   int64_t tile_begin, tile_end;  // this launch streams (virtual) corpus tiles [tile_begin, tile_end), CTA b takes tile_begin + b + i * grid
@@ -117,6 +119,12 @@ struct K2TParams {
   int last_pass;    // lists are reduced to k' and flushed to the arena at the end (else: lengths stored to cnt_g)
   int no_check;     // one tile per CTA (<= 128 entries per list, below cap): skip the overflow checks
   int est_only;     // estimate pass: nothing is appended, the CTA's best score per query goes to cnt_g (as a monotone key) instead
+  // threshold fold (bf16, ip): score - tau comes out of the tensor core, see k2t_stream_kernel
+  int fold;
+  const float* q_f32;         // [nq][ldq] the queries in fp32 (for |q|, the lower bound that stands in for a threshold of -inf)
+  int64_t ldq;
+  int dim;
+  const uint32_t* max_norm2;  // device word: float bits of max |row|^2
   const float* half_norm;
   SinkParams sink;
 };
@@ -194,8 +202,8 @@ int launch_k2(int store_dtype, const K2Params& p, int nq_t, int rw, int grid, si
 size_t k2_smem_bytes(int64_t ld, int elem_size, int nq_t, int rw, int stages);
 int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, int64_t q_ld, const void* corpus, int64_t ld, const K2TParams& p, int grid,
                cudaStream_t stream);
-size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages);
-int k2t_plan_stages(int kblocks, int nq_pad);
+size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages, int fold);
+int k2t_plan_stages(int kblocks, int nq_pad, int fold);
 int launch_seed_tau_lists(const Entry* cand, const uint32_t* cnt_g, int grid, int nq_pad, int cap, int k_fetch, uint32_t* tau_g, int nq,
                           cudaStream_t stream);
 int launch_seed_tau_est(const uint32_t* est_g, int grid, int nq_pad, int m, uint32_t* tau_g, int nq, cudaStream_t stream);

@@ -17,6 +17,14 @@
 
 namespace nxf {
 
+// Knock-out builds for locating the stage that paces the stream (tools/build_variant.sh k2t_koN "-DNXF_K2T_KNOCKOUT=N"; results are
+// wrong by construction, timing only):  1 = the epilogue only waits for and releases the accumulator buffers;  2 = it also reads
+// them (tcgen05.ld) but filters nothing;  3 = as 1, and the issuer issues no MMA (only the commits): TMA + barriers alone;
+// 5 = everything runs, but every threshold is +inf: the filter's cost without a single survivor.
+#ifndef NXF_K2T_KNOCKOUT
+#define NXF_K2T_KNOCKOUT 0
+#endif
+
 namespace k2t {
 constexpr int BLOCK_M = 128;   // corpus rows per tile
 constexpr int BLOCK_K = 64;
@@ -33,7 +41,8 @@ constexpr int MAX_STAGES = 12;
 constexpr int MAX_TBUF = 8;
 constexpr int MAX_NQ = 128;
 // shared memory after the 1024-aligned (queries | ring): barriers, tau, counts
-constexpr int TAIL_BYTES = (2 * MAX_STAGES + 2 * MAX_TBUF + 2) * 8 + 16 + MAX_NQ * 4 * 2;
+constexpr int TAIL_BYTES = (2 * MAX_STAGES + 2 * MAX_TBUF + 2) * 8 + 16 + MAX_NQ * 4 * 2 + 2 * MAX_NQ * 4;  // + tauv[2][MAX_NQ] (FOLD)
+constexpr int ONES_BYTES = BLOCK_M * 128;  // FOLD: the constant A' tile (128 rows x one 128-byte swizzle row)
 }  // namespace k2t
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
@@ -109,6 +118,36 @@ __device__ __forceinline__ void k2t_chunk(const uint32_t (&vr)[16], const TauSli
   }
 }
 
+// FOLD fast filter: the largest of 32 folded scores (11 FMNMX3 + 1 FMNMX, depth 4)
+__device__ __forceinline__ float k2t_max32(const uint32_t (&r)[32]) {
+  float m[11];
+#pragma unroll
+  for (int i = 0; i < 10; ++i) m[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+  m[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
+  const float a = fmax3(m[0], m[1], m[2]), b = fmax3(m[3], m[4], m[5]), c = fmax3(m[6], m[7], m[8]), d = fmaxf(m[9], m[10]);
+  return fmaxf(fmax3(a, b, c), d);
+}
+
+// FOLD: thread q's query threshold as three bf16 pieces t0 + t1 + t2 <= tau (the last one rounded down, so the folded threshold never
+// exceeds the true one: nothing that beats tau is filtered out), written as -t into row q of the B' tile (128-byte swizzled rows:
+// 16-byte chunk c of row r sits at chunk position c ^ (r % 8)), and their exact fp32 sum into tauv[q].
+__device__ __forceinline__ void k2t_write_fold(unsigned char* __restrict__ tile, float* __restrict__ tauv, int q, float tau, float lower) {
+  float t = fmaxf(tau, lower);               // -inf (no threshold yet) -> the Cauchy-Schwarz lower bound of any score of this query
+  if (!(t < 3.0e38f)) t = 3.0e38f;           // padded columns (+inf): nothing passes
+  const __nv_bfloat16 b0 = __float2bfloat16_rn(t);
+  const float r1 = t - __bfloat162float(b0);
+  const __nv_bfloat16 b1 = __float2bfloat16_rn(r1);
+  const float r2 = r1 - __bfloat162float(b1);
+  const __nv_bfloat16 b2 = __float2bfloat16_rd(r2);
+  tauv[q] = (__bfloat162float(b0) + __bfloat162float(b1)) + __bfloat162float(b2);   // exact: three disjoint 8-bit pieces
+  const uint32_t n0 = static_cast<uint32_t>(__bfloat16_as_ushort(b0)) ^ 0x8000u, n1 = static_cast<uint32_t>(__bfloat16_as_ushort(b1)) ^ 0x8000u;
+  const uint32_t n2 = static_cast<uint32_t>(__bfloat16_as_ushort(b2)) ^ 0x8000u;   // sign flipped: the tile holds -t
+  uint2 w;
+  w.x = n0 | (n1 << 16);
+  w.y = n2;
+  *reinterpret_cast<uint2*>(tile + (q >> 3) * 1024 + (q & 7) * 128 + ((q & 7) << 4)) = w;   // chunk 0 of row q: one 8-byte store
+}
+
 // Estimate pass: nothing is appended; the best score of this CTA's rows per query is kept (as a monotone key) in est_s.
 // One REDUX.MAX per query and warp, lane j keeps query j's maximum, 16 shared-memory atomics per slice.
 template <bool L2>
@@ -124,18 +163,28 @@ __device__ __forceinline__ void k2t_chunk_est(const uint32_t (&vr)[16], int ch, 
   if (lane < 16) atomicMax(&est_s[ch * 16 + lane], mine);
 }
 
-template <bool BF16, bool L2, int SETS>
+// FOLD (bf16, inner product, short rows; K2TParams::fold): one extra tcgen05.mma per tile, K = 16, of a constant A' tile (columns 0-2
+// of every corpus row = 1) against a B' tile holding -tau of every query as three bf16 pieces, so the accumulator ends as
+// score - tau and the epilogue's filter needs neither the thresholds nor a subtraction.  The issuer runs up to `tbufs` tiles ahead of
+// the epilogue, so B' exists in two versions: the tiles of round R (round = SETS * check_every tiles) use version R & 1, and the
+// thresholds the epilogue agrees on at the end of round R are written into version R & 1 -- whose tiles are all consumed by then --
+// for round R + 2.  The threshold the filter sees is therefore up to two rounds old (a few more appends, never a wrong result).
+template <bool BF16, bool L2, int SETS, bool FOLD>
 __global__ void __launch_bounds__(k2t::threads(SETS), 1)
 k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c, K2TParams p) {
   using namespace k2t;
   constexpr int EPI_SETS = SETS;
+  static_assert(!FOLD || (BF16 && !L2), "the threshold fold is built for bf16 rows and the inner-product metric");
   extern __shared__ unsigned char smem_raw[];
   // 1024-byte alignment by pointer arithmetic on the shared array itself (an integer round trip would make every later access generic)
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int q_bytes = p.kblocks * p.nq_pad * 128;          // resident queries: [kblocks][nq_pad rows][128 B], 1024-aligned blocks
   unsigned char* q_smem = smem;
   unsigned char* ring = smem + ((q_bytes + 1023) & ~1023);
-  unsigned char* tail = ring + p.stages * A_BYTES;
+  unsigned char* ones_tile = ring + p.stages * A_BYTES;                       // FOLD only: [128][128 B]
+  const int tq_bytes = FOLD ? ((p.nq_pad * 128 + 1023) & ~1023) : 0;
+  unsigned char* tauq_tile = ones_tile + (FOLD ? ONES_BYTES : 0);             // FOLD only: two versions of [nq_pad][128 B]
+  unsigned char* tail = tauq_tile + 2 * tq_bytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty = full + MAX_STAGES;
   uint64_t* tfull = empty + MAX_STAGES;
@@ -144,6 +193,8 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   uint32_t* tmem_ptr_s = reinterpret_cast<uint32_t*>(qfull + 2);
   float* tau_s = reinterpret_cast<float*>(tmem_ptr_s + 4);  // [MAX_NQ]
   int* cnt_s = reinterpret_cast<int*>(tau_s + MAX_NQ);      // [MAX_NQ]
+  float* tauv = reinterpret_cast<float*>(cnt_s + MAX_NQ);   // FOLD: [2][MAX_NQ] folded thresholds of the two versions
+  float fold_lower = -INFINITY;                             // FOLD, thread q < nq: -(|q| * max|c|) * 1.01, below every score of query q
 
   if (p.run_flag != nullptr && ld_relaxed_u32(p.run_flag) == 0u) return;  // uniform over the grid: written by an earlier kernel
   const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
@@ -157,15 +208,49 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int b = 0; b < p.tbufs; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
+    for (int b = 0; b < p.tbufs; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4 * p.col_split); }
     mbar_init(qfull, 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<1>(tmem_ptr_s, TMEM_COLS);
   if (threadIdx.x < MAX_NQ) {
+#if NXF_K2T_KNOCKOUT == 5   // the whole filter runs, nothing ever passes it
+    tau_s[threadIdx.x] = INFINITY;
+#else
     tau_s[threadIdx.x] = (static_cast<int>(threadIdx.x) < p.nq) ? tau_load(p.sink.tau_g, threadIdx.x) : INFINITY;  // padded columns accept nothing
+#endif
     cnt_s[threadIdx.x] = (p.first_pass || static_cast<int>(threadIdx.x) >= p.nq)
                              ? 0 : static_cast<int>(p.cnt_g[static_cast<int64_t>(blockIdx.x) * p.nq_pad + threadIdx.x]);
+  }
+  if (FOLD) {
+    // zero the three tiles, set the ones columns, fold the initial thresholds into both versions
+    uint4* z = reinterpret_cast<uint4*>(ones_tile);
+    const int n16 = (ONES_BYTES + 2 * tq_bytes) / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    if (threadIdx.x < BLOCK_M) {
+      const int r = threadIdx.x;
+      uint2 w;
+      w.x = 0x3F803F80u;   // bf16 1.0, 1.0
+      w.y = 0x00003F80u;   // 1.0, 0
+      *reinterpret_cast<uint2*>(ones_tile + (r >> 3) * 1024 + (r & 7) * 128 + ((r & 7) << 4)) = w;
+    }
+    if (threadIdx.x < MAX_NQ && static_cast<int>(threadIdx.x) < p.nq_pad) {
+      const int q = threadIdx.x;
+      if (q < p.nq) {
+        float ss = 0.f;
+        const float4* qr = reinterpret_cast<const float4*>(p.q_f32 + static_cast<int64_t>(q) * p.ldq);   // rows are zero padded to ldq
+#pragma unroll 8
+        for (int d = 0; d < p.kblocks * 16; ++d) {
+          const float4 x = qr[d];
+          ss += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+        }
+        fold_lower = -(sqrtf(ss) * sqrtf(__uint_as_float(*p.max_norm2)) * 1.01f + 1e-30f);
+      }
+      k2t_write_fold(tauq_tile, tauv, q, tau_s[q], fold_lower);
+      k2t_write_fold(tauq_tile + tq_bytes, tauv + MAX_NQ, q, tau_s[q], fold_lower);
+    }
+    fence_proxy_async();
   }
   tc_fence_before();
   __syncthreads();
@@ -187,7 +272,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       const int32_t row0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_M);
       for (int kb = 0; kb < p.kblocks; ++kb) {
         mbar_wait(&empty[s], ph ^ 1);
-        if (lane == 0) {
+        if (elect_one()) {
           mbar_expect_tx(&full[s], A_BYTES);
           tma_load_2d(&tmap_c, &full[s], ring + s * A_BYTES, kb * BLOCK_K, row0, kEvictFirst);
         }
@@ -195,38 +280,67 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    // ============================== MMA issuer ==============================
-    // Lane 0 paces the whole stream on short rows (one K block per tile: a tile every ~700 clocks at HBM speed), so the per-tile
-    // instruction chain is kept short: running counters instead of divisions, descriptors advanced by addition, warp-uniform loop.
+  } else if (warp == 1 || (warp == 3 && p.issuers == 2)) {
+    // ============================== MMA issuers ==============================
+    // The issuing thread paces the whole stream on short rows (one K block per tile: a tile every ~700 clocks at HBM speed), so the
+    // per-tile instruction chain is kept short: running counters instead of divisions, descriptors advanced by addition, warp-uniform
+    // loop.  It is still ~120 dependent instructions per tile (two barrier waits, the elect loops nvcc wraps around every
+    // tcgen05 instruction, the uniform-datapath address arithmetic): ~800 clocks with sixteen epilogue warps competing for the issue
+    // slots, i.e. the tile period the profile of the one-issuer kernel showed at 128 queries (profiles/r2_k2t_issuer.md).  Two
+    // warps therefore issue alternate tiles (the tiles are independent: own accumulator buffer, own ring stages, own commits).
+    // Only with stages >= 2 * kblocks (K2TParams::issuers, set by the host): a parity wait is only meaningful one phase ahead of the
+    // barrier, and the second issuer's first wait is on ring position kblocks .. 2 * kblocks - 1 while nothing has been loaded yet.
+    const uint32_t me = warp == 1 ? 0u : 1u;
+    const uint32_t n_iss = static_cast<uint32_t>(p.issuers);
     const uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M, p.nq_pad);
     mbar_wait(qfull, 0);
     tc_fence_after();
+    // this issuer's first tile is tile `me` of the CTA: ring stage (me * kblocks) % stages, accumulator buffer me
     int s = 0;
     uint32_t ph = 0;
-    uint32_t b = 0, bph = 0;
+    for (uint32_t i = 0; i < me * static_cast<uint32_t>(p.kblocks); ++i) if (++s == p.stages) { s = 0; ph ^= 1; }
+    uint32_t b = me, bph = 0;   // tbufs is even (4 or 8): the buffers alternate between the issuers as the tiles do
     const uint64_t a_desc0 = umma_desc_sw128(smem_u32(ring));          // stage s: + s * (A_BYTES >> 4) in the address field
     const uint64_t b_desc0 = umma_desc_sw128(smem_u32(q_smem));        // query block qb: + qb * (nq_pad * 128 >> 4)
     const uint32_t q_blk = static_cast<uint32_t>(p.nq_pad) * 8u;
-    for (int64_t t = t_first; t < t_end; t += gridDim.x) {
+    const uint64_t ones_desc = umma_desc_sw128(smem_u32(ones_tile));
+    const uint64_t tauq_desc0 = umma_desc_sw128(smem_u32(tauq_tile));  // version v: + v * (tq_bytes >> 4)
+    const uint32_t fold_round = static_cast<uint32_t>(EPI_SETS) * static_cast<uint32_t>(p.check_every);
+    uint32_t in_round = me, fold_ver = 0;   // position of this issuer's tile in its round (fold_round >= 2)
+    for (int64_t t = t_first + static_cast<int64_t>(me) * gridDim.x; t < t_end; t += static_cast<int64_t>(n_iss) * gridDim.x) {
       mbar_wait(&tempty[b], bph ^ 1);
       const uint32_t d_tmem = tmem_base + b * p.tbuf_stride;
       for (int kb = 0; kb < p.kblocks; ++kb) {
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {
           const uint64_t a_desc = a_desc0 + static_cast<uint32_t>(s) * static_cast<uint32_t>(A_BYTES >> 4);
           const uint64_t b_desc = b_desc0 + static_cast<uint32_t>(kb) * q_blk;
+#if NXF_K2T_KNOCKOUT != 3
           umma_f16<1>(d_tmem, a_desc, b_desc, idesc, kb != 0 ? 1u : 0u);
 #pragma unroll
           for (int k4 = 1; k4 < BLOCK_K / UMMA_K; ++k4) umma_f16<1>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, 1u);
+#endif
           umma_commit<1>(&empty[s]);
-          if (kb == p.kblocks - 1) umma_commit<1>(&tfull[b]);
+          if (kb == p.kblocks - 1) {
+            if (FOLD) umma_f16<1>(d_tmem, ones_desc, tauq_desc0 + fold_ver * static_cast<uint32_t>(tq_bytes >> 4), idesc, 1u);   // += -tau
+            umma_commit<1>(&tfull[b]);
+          }
         }
         __syncwarp();
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
-      if (++b == static_cast<uint32_t>(p.tbufs)) { b = 0; bph ^= 1; }
+      // two issuers: skip the other one's tile -- its ring stages, its accumulator buffer, its place in the round
+      if (n_iss == 2) {
+        s += p.kblocks;
+        while (s >= p.stages) { s -= p.stages; ph ^= 1; }
+      }
+      if (FOLD) {
+        in_round += n_iss;
+        while (in_round >= fold_round) { in_round -= fold_round; fold_ver ^= 1u; }
+      }
+      b += n_iss;
+      if (b >= static_cast<uint32_t>(p.tbufs)) { b -= static_cast<uint32_t>(p.tbufs); bph ^= 1; }
     }
     __syncwarp();
   } else if (warp >= EPI_WARP0) {
@@ -236,7 +350,13 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // tiles at a named barrier, where the lists that could overflow are pruned while nobody appends.
     const int ew8 = warp - EPI_WARP0;  // 0..7
     const int ew = ew8 & 3;            // == warp % 4: the TMEM lane quarter this warp may read
-    const int set = ew8 >> 2;
+    // col_split == 2 (K2TParams): two warp groups share a tile, each filtering half of its query slices, so a tile occupies its
+    // accumulator buffer half as long and only EPI_SETS / 2 buffers are being read at any time -- with 128 queries there are four
+    // buffers in all, and four sets reading four tiles left the issuer no buffer to compute ahead into: every set then idled for a
+    // release -> MMA -> commit round trip per tile (a quarter of the epilogue's time in the profile).
+    const int tsets = EPI_SETS / p.col_split;     // groups of warps that take whole tiles in turn
+    const int set = (ew8 >> 2) / p.col_split;
+    const int half = (ew8 >> 2) % p.col_split;
     const int et = ew * 32 + static_cast<int>(lane);   // 0..127: corpus row within the tile
     const int eq = ew8 * 32 + static_cast<int>(lane);  // 0..255: the query this thread looks after (if < nq)
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
@@ -244,7 +364,9 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int k = p.sink.k;
     Entry* cta_cand = p.sink.cand + static_cast<int64_t>(blockIdx.x) * p.nq_pad * cap;  // [nq_pad][cap]
     uint32_t* cand_words = reinterpret_cast<uint32_t*>(cta_cand);
-    const int chunks = p.nq_pad / 16;
+    const int chunks_all = p.nq_pad / 16;
+    const int cpw = (chunks_all + p.col_split - 1) / p.col_split;
+    const int ch_begin = half * cpw, chunks = min(chunks_all, ch_begin + cpw);   // this warp's query slices [ch_begin, chunks)
     const uint32_t round_tiles = static_cast<uint32_t>(EPI_SETS) * static_cast<uint32_t>(p.check_every);  // tiles between two overflow checks / threshold refreshes
     // a list gains <= 128 entries per tile, i.e. <= 128 * round_tiles between two checks, and the counts read at a check are
     // exact (every appender has arrived at the barrier): cap - full_mark = one round of appends
@@ -255,9 +377,11 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // across rounds), kept as running counters: iter % tbufs and iter / tbufs are runtime divisions otherwise
     uint32_t b = static_cast<uint32_t>(set) % static_cast<uint32_t>(p.tbufs), bph = (static_cast<uint32_t>(set) / static_cast<uint32_t>(p.tbufs)) & 1u;
 
-    for (uint32_t r0 = 0; r0 < n_it; r0 += round_tiles) {
+    uint32_t ver = 0;   // FOLD: version of the folded thresholds the tiles of this round were computed with
+    for (uint32_t r0 = 0; r0 < n_it; r0 += round_tiles, ver ^= 1u) {
       const uint32_t r1 = min(n_it, r0 + round_tiles);
-      for (uint32_t iter = r0 + set; iter < r1; iter += EPI_SETS) {  // r0 is a multiple of EPI_SETS: iter % EPI_SETS is the set
+      const float* tv = tauv + ver * MAX_NQ;
+      for (uint32_t iter = r0 + set; iter < r1; iter += tsets) {  // r0 is a multiple of EPI_SETS, hence of tsets: iter % tsets is the set
         const int64_t t = t_first + static_cast<int64_t>(iter) * gridDim.x;
         const int64_t row = perm_tile(p.perm, t) * BLOCK_M + et;
         const bool row_ok = row < p.n;
@@ -265,11 +389,86 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         mbar_wait(&tfull[b], bph);
         tc_fence_after();
         const uint32_t tbase = taddr + b * p.tbuf_stride;
+        if constexpr (FOLD) {
+          // Folded thresholds: a row has a survivor iff the largest of its nq_pad values is positive, so the common case is one
+          // compare per ROW, not per 16-query slice: 32-column loads (the next one in flight while a block is reduced), a max tree
+          // per block, one warp vote.  (Knock-out builds, profiles/r2_k2t_knockout.md: with no survivors at all the per-slice filter
+          // adds 65 us to the 204 us the stream takes with the filter compiled out, this one 30 us.)
+          uint32_t fa[32], fb[32];
+          const int ncol = p.nq_pad;   // a multiple of 32 (host), <= 128
+          float m0, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+          tmem_ld32(tbase, fa);
+          tmem_ld_wait_dep(fa);
+          if (ncol > 32) tmem_ld32(tbase + 32, fb);
+          m0 = k2t_max32(fa);
+          if (ncol > 32) {
+            tmem_ld_wait_dep(fb);
+            if (ncol > 64) tmem_ld32(tbase + 64, fa);
+            m1 = k2t_max32(fb);
+          }
+          if (ncol > 64) {
+            tmem_ld_wait_dep(fa);
+            if (ncol > 96) tmem_ld32(tbase + 96, fb);
+            m2 = k2t_max32(fa);
+          }
+          if (ncol > 96) {
+            tmem_ld_wait_dep(fb);
+            m3 = k2t_max32(fb);
+          }
+          // which 32-query blocks hold a survivor for some row of this warp (about one warp in eight on the main pass, then
+          // usually a single block): only those are read again -- and the buffer goes back to the issuer as soon as the last
+          // of them is in registers, before the appends (shared-memory atomic + two global stores per survivor)
+          const bool h0 = row_ok && m0 > 0.f, h1 = row_ok && m1 > 0.f, h2 = row_ok && m2 > 0.f, h3 = row_ok && m3 > 0.f;
+          uint32_t hb = 0;
+          if (__any_sync(kFullMask, h0 || h1 || h2 || h3)) {
+            hb = (__any_sync(kFullMask, h0) ? 1u : 0u) | (__any_sync(kFullMask, h1) ? 2u : 0u) | (__any_sync(kFullMask, h2) ? 4u : 0u) |
+                 (__any_sync(kFullMask, h3) ? 8u : 0u);
+          }
+          if (hb == 0u) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[b]);
+          }
+          while (hb != 0u) {   // warp-uniform
+            const int blk = __ffs(hb) - 1;
+            hb &= hb - 1u;
+            tmem_ld32(tbase + blk * 32, fa);
+            tmem_ld_wait_dep(fa);
+            if (hb == 0u) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&tempty[b]);
+            }
+            const bool mine = blk == 0 ? h0 : (blk == 1 ? h1 : (blk == 2 ? h2 : h3));
+            if (mine) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const float d = __uint_as_float(fa[j]);
+                if (d > 0.f) {
+                  const int qi = blk * 32 + j;
+                  const int pos = atomicAdd(&cnt_s[qi], 1);
+                  NXF_DEV_CHECK(pos < cap, "K2T per-(CTA, query) list overflow");
+                  const uint32_t w = static_cast<uint32_t>(qi * cap + pos);
+                  cand_words[2 * static_cast<uint64_t>(w)] = __float_as_uint(d + tv[qi]);
+                  cand_words[2 * static_cast<uint64_t>(w) + 1] = static_cast<uint32_t>(row);
+                }
+              }
+            }
+            __syncwarp();
+          }
+        } else {
         // two register buffers: the tcgen05.ld of slice ch+1 is in flight while slice ch is filtered
         uint32_t va[16], vb[16];
-        tmem_ld16(tbase, va);
+#if NXF_K2T_KNOCKOUT == 1 || NXF_K2T_KNOCKOUT == 3
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[b]);
+        for (int ch = chunks; ch < chunks; ch += 2) {
+#else
+        tmem_ld16(tbase + ch_begin * 16, va);
 #pragma unroll 1
-        for (int ch = 0; ch < chunks; ch += 2) {
+        for (int ch = ch_begin; ch < chunks; ch += 2) {
+#endif
           const TauSlice ta = k2t_load_tau(tau_s, ch);
           tmem_ld_wait_dep16(va);
           const bool more = ch + 1 < chunks;
@@ -279,8 +478,10 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[b]);
           }
+#if NXF_K2T_KNOCKOUT == 0 || NXF_K2T_KNOCKOUT == 5
           if (p.est_only) k2t_chunk_est<L2>(va, ch, hn, row_ok, reinterpret_cast<uint32_t*>(cnt_s), lane);
           else k2t_chunk<L2>(va, ta, ch, hn, row, row_ok, cnt_s, cand_words, cap);
+#endif
           if (more) {
             const TauSlice tb = k2t_load_tau(tau_s, ch + 1);
             tmem_ld_wait_dep16(vb);
@@ -290,11 +491,14 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
               __syncwarp();
               if (lane == 0) mbar_arrive(&tempty[b]);
             }
+#if NXF_K2T_KNOCKOUT == 0 || NXF_K2T_KNOCKOUT == 5
             if (p.est_only) k2t_chunk_est<L2>(vb, ch + 1, hn, row_ok, reinterpret_cast<uint32_t*>(cnt_s), lane);
             else k2t_chunk<L2>(vb, tb, ch + 1, hn, row, row_ok, cnt_s, cand_words, cap);
+#endif
           }
         }
-        b += EPI_SETS;
+        }  // !FOLD
+        b += static_cast<uint32_t>(tsets);
         while (b >= static_cast<uint32_t>(p.tbufs)) { b -= static_cast<uint32_t>(p.tbufs); bph ^= 1u; }
       }
       if (p.no_check) continue;
@@ -319,6 +523,11 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       if (eq < p.nq) {
         if (tau_next > tau_s[eq]) tau_s[eq] = tau_next;
         tau_next = tau_load(p.sink.tau_g, eq);
+        if (FOLD) {
+          // this round's version is free (every tile computed with it has been consumed): it becomes the thresholds of round R + 2
+          k2t_write_fold(tauq_tile + ver * tq_bytes, tauv + ver * MAX_NQ, eq, tau_s[eq], fold_lower);
+          fence_proxy_async();
+        }
       }
     }
 
@@ -352,15 +561,16 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 // ---------------------------------------------------------------------------------------------
 int make_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, int64_t ld, int box_rows, bool bf16);  // search_tc.cu
 
-size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages) {
+size_t k2t_smem_bytes(int kblocks, int nq_pad, int stages, int fold) {
   const size_t q_bytes = (static_cast<size_t>(kblocks) * nq_pad * 128 + 1023) & ~size_t(1023);
-  return 1024 + q_bytes + static_cast<size_t>(stages) * k2t::A_BYTES + k2t::TAIL_BYTES;
+  const size_t fold_bytes = fold ? k2t::ONES_BYTES + 2 * ((static_cast<size_t>(nq_pad) * 128 + 1023) & ~size_t(1023)) : 0;
+  return 1024 + q_bytes + static_cast<size_t>(stages) * k2t::A_BYTES + fold_bytes + k2t::TAIL_BYTES;
 }
 
 // Picks the ring depth; returns 0 when the resident queries leave room for fewer than 4 stages (caller uses K1 instead).
-int k2t_plan_stages(int kblocks, int nq_pad) {
+int k2t_plan_stages(int kblocks, int nq_pad, int fold) {
   for (int st = k2t::MAX_STAGES; st >= 4; --st)
-    if (k2t_smem_bytes(kblocks, nq_pad, st) <= 227 * 1024) return st;
+    if (k2t_smem_bytes(kblocks, nq_pad, st, fold) <= 227 * 1024) return st;
   return 0;
 }
 
@@ -373,14 +583,17 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, int64_t q_ld, 
   if (rc) return rc;
   rc = make_tmap_2d_sw128(&tc, corpus, p.n, ld, k2t::BLOCK_M, bf16);
   if (rc) return rc;
-  const size_t smem = k2t_smem_bytes(p.kblocks, p.nq_pad, p.stages);
   const bool l2 = p.half_norm != nullptr;
-#define NXF_K2T_LAUNCH3(B, L, S)                                                                                                      \
+  const bool fold = p.fold && !p.est_only;   // the estimate pass has no thresholds to fold (same shared-memory budget either way)
+  if (p.fold && (!bf16 || l2 || !p.q_f32 || !p.max_norm2)) { set_error("k2t: the threshold fold needs bf16 rows, the ip metric, q_f32 and max_norm2"); return NXF_EINVAL; }
+  const size_t smem = k2t_smem_bytes(p.kblocks, p.nq_pad, p.stages, p.fold);
+#define NXF_K2T_LAUNCH4(B, L, S, F)                                                                                                   \
   do {                                                                                                                                \
-    rc = ensure_dyn_smem(reinterpret_cast<const void*>(k2t_stream_kernel<B, L, S>), static_cast<int>(smem));                          \
+    rc = ensure_dyn_smem(reinterpret_cast<const void*>(k2t_stream_kernel<B, L, S, F>), static_cast<int>(smem));                       \
     if (rc) return rc;                                                                                                                \
-    k2t_stream_kernel<B, L, S><<<grid, k2t::threads(S), smem, stream>>>(tq, tc, p);                                                   \
+    k2t_stream_kernel<B, L, S, F><<<grid, k2t::threads(S), smem, stream>>>(tq, tc, p);                                                \
   } while (0)
+#define NXF_K2T_LAUNCH3(B, L, S) NXF_K2T_LAUNCH4(B, L, S, false)
 #define NXF_K2T_LAUNCH(B, L)                     \
   do {                                           \
     if (p.epi_sets == 2) NXF_K2T_LAUNCH3(B, L, 2);      \
@@ -388,12 +601,17 @@ int launch_k2t(int store_dtype, const void* q16, int64_t nq_rows, int64_t q_ld, 
     else NXF_K2T_LAUNCH3(B, L, 4);                      \
   } while (0)
   if (p.epi_sets < 2 || p.epi_sets > 4) { set_error("k2t: %d epilogue sets (2..4)", p.epi_sets); return NXF_EINVAL; }
-  if (bf16 && l2) NXF_K2T_LAUNCH(true, true);
+  if (fold) {
+    if (p.epi_sets == 2) NXF_K2T_LAUNCH4(true, false, 2, true);
+    else if (p.epi_sets == 3) NXF_K2T_LAUNCH4(true, false, 3, true);
+    else NXF_K2T_LAUNCH4(true, false, 4, true);
+  } else if (bf16 && l2) NXF_K2T_LAUNCH(true, true);
   else if (bf16) NXF_K2T_LAUNCH(true, false);
   else if (l2) NXF_K2T_LAUNCH(false, true);
   else NXF_K2T_LAUNCH(false, false);
 #undef NXF_K2T_LAUNCH
 #undef NXF_K2T_LAUNCH3
+#undef NXF_K2T_LAUNCH4
   NXF_CUDA(cudaGetLastError());
   return NXF_OK;
 }

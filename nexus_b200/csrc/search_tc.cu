@@ -211,7 +211,11 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 
   if (warp == 0) {
     // ============================== TMA producer ==============================
-    if (lane == 0) {
+    // The whole warp runs the loops and waits on the barriers; one elected lane issues.  With the loop inside `if (lane == 0)` nvcc
+    // wraps every TMA / tcgen05 instruction (uniform-datapath operands in a divergent region) in an elect-and-retry loop of five
+    // dependent instructions; under elect.sync it emits them back to back -- on 128-byte rows, where one K block is a whole tile,
+    // that chain paced the stream (profiles/r2_k2t_knockout.md).
+    {
       int s = 0;
       uint32_t ph = 0;
       int64_t ri = 0;
@@ -220,7 +224,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           // soft round barrier: wait until (on average) every cluster finished issuing round ri - window; bounded spin, so a
           // cluster that is not resident (foreign kernels on some SMs) costs lockstep, never progress
           const uint32_t want = static_cast<uint32_t>(num_clusters * (ri - p.sync_window + 1));
-          for (int spin = 0; spin < 20000 && ld_relaxed_u32(p.sync_ctr) < want; ++spin) __nanosleep(100);
+          for (int spin = 0; spin < 20000 && __shfl_sync(kFullMask, ld_relaxed_u32(p.sync_ctr), 0) < want; ++spin) __nanosleep(100);
         }
         const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
         for (int64_t pos = rp.a; pos < rp.b;) {
@@ -246,30 +250,33 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 }
               }
               mbar_wait(&empty[s], ph ^ 1);
-              if (NXF_K1_DBG(p.debug, 4)) {  // pipeline timing only: no loads, the MMAs run on whatever the ring holds
-                if (CG == 1 || rank == 0) mbar_arrive(&full[s]); else mbar_arrive_cluster(&full[s], 0);
-              } else if (CG == 1) {
-                mbar_expect_tx(&full[s], C::STAGE_BYTES);
-                tma_load_2d(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
-                tma_load_2d(cm, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
-              } else {
-                tma_load_2d_2sm(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
-                tma_load_2d_2sm(cm, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
-                if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
-                else mbar_arrive_cluster(&full[s], 0);
+              if (elect_one()) {
+                if (NXF_K1_DBG(p.debug, 4)) {  // pipeline timing only: no loads, the MMAs run on whatever the ring holds
+                  if (CG == 1 || rank == 0) mbar_arrive(&full[s]); else mbar_arrive_cluster(&full[s], 0);
+                } else if (CG == 1) {
+                  mbar_expect_tx(&full[s], C::STAGE_BYTES);
+                  tma_load_2d(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
+                  tma_load_2d(cm, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
+                } else {
+                  tma_load_2d_2sm(&tmap_q, &full[s], a_ptr(s), q_col, q_row0, kEvictLast);
+                  tma_load_2d_2sm(cm, &full[s], b_ptr(s), c_col, c_row0, kEvictNormal);
+                  if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
+                  else mbar_arrive_cluster(&full[s], 0);
+                }
               }
+              __syncwarp();
               if (++s == C::STAGES) { s = 0; ph ^= 1; }
             }
           }
           pos = qt * rp.R + hi;
         }
-        if (p.sync_window > 0 && rank == 0) red_relaxed_add_u32(p.sync_ctr, 1u);
+        if (p.sync_window > 0 && rank == 0 && lane == 0) red_relaxed_add_u32(p.sync_ctr, 1u);
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // ============================== MMA issuer ==============================
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {   // all 32 lanes: warp-uniform loops, one elected lane issues (see the producer)
       constexpr uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M * CG, BLOCK_N);
       int s = 0;
       uint32_t ph = 0;
@@ -286,17 +293,20 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             tc_fence_after();
             const uint64_t a_desc = umma_desc_sw128(smem_u32(a_ptr(s)));
             const uint64_t b_desc = umma_desc_sw128(smem_u32(b_ptr(s)));
-            if (!NXF_K1_DBG(p.debug, 8)) {
+            if (elect_one()) {
+              if (!NXF_K1_DBG(p.debug, 8)) {
 #pragma unroll
-              for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) {
-                // advance 16 elements = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
-                umma_f16<CG>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, (kb | k4) != 0 ? 1u : 0u);
+                for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4) {
+                  // advance 16 elements = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
+                  umma_f16<CG>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc, (kb | k4) != 0 ? 1u : 0u);
+                }
               }
+              umma_commit<CG>(&empty[s]);  // smem stage reusable once these MMAs retire
+              if (kb == p.kblocks - 1) umma_commit<CG>(&tfull[as]);   // accumulator complete -> epilogue
             }
-            umma_commit<CG>(&empty[s]);  // smem stage reusable once these MMAs retire
+            __syncwarp();
             if (++s == C::STAGES) { s = 0; ph ^= 1; }
           }
-          umma_commit<CG>(&tfull[as]);   // accumulator complete -> epilogue
         }
       }
       // do not tear the barriers down while the last remote arrivals may still be in flight
