@@ -1035,6 +1035,8 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
       if (P.seg_mode) { kp.split_kb = kp.kblocks; kp.kblocks *= (P.seg_mode == 1 ? 3 : 2); }
       kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group));
       kp.epi_sets = P.epi_sets;
+      // short rows: the accumulator in two halves, so that a set never waits for the whole MMA of its next tile
+      kp.split = (P.epi_sets == 2 && kp.kblocks <= 2 && env_int("NXF_K1_SPLIT", 1) != 0) ? 1 : 0;
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
       kp.est_only = 0;

@@ -78,6 +78,7 @@ struct K1Params {
   const float* half_norm;
   uint32_t* prof;      // debug bit5: 4 x uint64 {prunes, prune cycles, end-merge cycles, warps} summed over epilogue warps
   int est_only;  // estimate-only pass: a slice that beats the row's threshold records its maximum instead of its scores
+  int split;  // 1: two sets, <= 2 K blocks per tile: accumulators computed and handed over as 128-column halves (search_tc.cu SPLIT)
   int debug;  // timing experiments (only in builds with -DNXF_K1_DEBUG_BUILD=1): bit0 epilogue skips the selection; bit1 also skips the TMEM loads; bit2 producer issues no TMA;
               // bit3 issuer issues no MMA; bit4 epilogue computes the maxima but never appends
   SinkParams sink;

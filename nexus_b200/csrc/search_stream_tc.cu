@@ -372,7 +372,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // exact (every appender has arrived at the barrier): cap - full_mark = one round of appends
     const int full_mark = cap - static_cast<int>(round_tiles) * BLOCK_M;
     const uint32_t n_it = t_first < t_end ? static_cast<uint32_t>((t_end - t_first + gridDim.x - 1) / gridDim.x) : 0u;
-    float tau_next = (eq < p.nq) ? tau_load(p.sink.tau_g, eq) : INFINITY;
+    uint32_t tau_next_key = (eq < p.nq) ? tau_load_key(p.sink.tau_g, eq) : 0u;   // raw key until used (sink.cuh)
     // accumulator buffer and phase of this set's next tile (iter = set, set + 2, ...: round_tiles is even, so the sequence runs on
     // across rounds), kept as running counters: iter % tbufs and iter / tbufs are runtime divisions otherwise
     uint32_t b = static_cast<uint32_t>(set) % static_cast<uint32_t>(p.tbufs), bph = (static_cast<uint32_t>(set) / static_cast<uint32_t>(p.tbufs)) & 1u;
@@ -521,8 +521,9 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
       // other CTAs' progress: thread eq looks after query eq (value loaded one round ago)
       if (eq < p.nq) {
+        const float tau_next = tau_from_key(tau_next_key);
         if (tau_next > tau_s[eq]) tau_s[eq] = tau_next;
-        tau_next = tau_load(p.sink.tau_g, eq);
+        tau_next_key = tau_load_key(p.sink.tau_g, eq);
         if (FOLD) {
           // this round's version is free (every tile computed with it has been consumed): it becomes the thresholds of round R + 2
           k2t_write_fold(tauq_tile + ver * tq_bytes, tauv + ver * MAX_NQ, eq, tau_s[eq], fold_lower);

@@ -59,8 +59,8 @@ template <int CG> struct Cfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (CG == 1) ? 4 : 6;
   static constexpr int RING_BYTES = STAGES * STAGE_BYTES;  // 192 KB either way
-  // ring | full[STAGES] empty[STAGES] tfull[2] tempty[2] | tmem ptr
-  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8;
+  // ring | full[STAGES] empty[STAGES] tfull[4] tempty[4] | tmem ptr   (SPLIT kernels use all four of each, the others two)
+  static constexpr int BAR_BYTES = (2 * STAGES + 8) * 8;
   static constexpr int SMEM_BYTES = 1024 /*align slack*/ + RING_BYTES + BAR_BYTES + 16;
 };
 }  // namespace k1
@@ -167,7 +167,13 @@ __device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0,
 // dependent-issue latency; the MMAs of a tile take 512 clocks per K block, so from 7 K blocks on (D >= 448) one set hides behind the
 // tensor pipe.  Shorter rows get a second set on the other TMEM buffer (set s filters the tiles with iter % 2 == s), with its own
 // per-row thresholds, counters and candidate buffers -- to the rest of the search it is one more owner of the query.
-template <int CG, bool BF16, int SETS>
+// SPLIT (rows of one or two K blocks, two sets): each 256-column accumulator is computed and handed over as two 128-column halves
+// with their own full / empty barriers (two N = 128 MMAs per K step instead of one N = 256).  With one buffer per set, a set that
+// hands its buffer back then waits for the whole MMA of its next tile (19 % of the epilogue's samples on 64-d rows); with halves, the
+// MMA of the next tile's first half runs while the set is still filtering this tile's second half.  Under cta_group::2 each CTA holds
+// half of the tile's corpus rows, so half h of the accumulator is corpus rows [64 h, 64 h + 64) of BOTH CTAs' slices: columns
+// 0-63 = rows 64 h .. of the tile, columns 64-127 = rows 128 + 64 h .. (cta_group::1: rows 128 h .. 128 h + 127).
+template <int CG, bool BF16, int SETS, bool SPLIT>
 __global__ void __launch_bounds__(128 + 128 * SETS, 1)
 k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_c,
                  const __grid_constant__ CUtensorMap tmap_c2, K1Params p) {
@@ -179,8 +185,8 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::RING_BYTES);
   uint64_t* empty = full + C::STAGES;
   uint64_t* tfull = empty + C::STAGES;
-  uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_ptr_s = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* tempty = tfull + 4;
+  uint32_t* tmem_ptr_s = reinterpret_cast<uint32_t*>(tempty + 4);
 
   if (p.run_flag != nullptr && ld_relaxed_u32(p.run_flag) == 0u) return;  // uniform over the grid: written by an earlier kernel
   const int warp = __shfl_sync(kFullMask, threadIdx.x >> 5, 0);
@@ -197,7 +203,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full[s], CG); mbar_init(&empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], CG * EPI_WARPS); }
+    for (int a = 0; a < 4; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], CG * EPI_WARPS); }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<CG>(tmem_ptr_s, TMEM_COLS);
@@ -278,6 +284,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     // ============================== MMA issuer ==============================
     if (rank == 0) {   // all 32 lanes: warp-uniform loops, one elected lane issues (see the producer)
       constexpr uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M * CG, BLOCK_N);
+      constexpr uint32_t idesc_half = umma_idesc_f16(BF16, BLOCK_M * CG, BLOCK_N / 2);
       int s = 0;
       uint32_t ph = 0;
       uint32_t iter = 0;
@@ -285,6 +292,36 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const RoundPiece rp = round_piece(p, r0, cluster_id, num_clusters);
         for (int64_t i = rp.a; i < rp.b; ++i, ++iter) {  // one accumulator tile per line position, whatever its query tile
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
+          if constexpr (SPLIT) {
+            // kblocks <= 2 <= STAGES (host): all K blocks of the tile are resident at once, so the ring positions are walked twice,
+            // once per half; the stages go back to the producer with the second half's MMAs
+            const int s0 = s;
+            const uint32_t ph0 = ph;
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+              mbar_wait(&tempty[as * 2 + h], aph ^ 1);
+              tc_fence_after();
+              const uint32_t d_tmem = tmem_base + as * BLOCK_N + h * (BLOCK_N / 2);
+              s = s0; ph = ph0;
+              for (int kb = 0; kb < p.kblocks; ++kb) {
+                mbar_wait(&full[s], ph);
+                tc_fence_after();
+                const uint64_t a_desc = umma_desc_sw128(smem_u32(a_ptr(s)));
+                // this CTA's rows of the half: LOAD_N / 2 rows of 128 bytes further into its B tile
+                const uint64_t b_desc = umma_desc_sw128(smem_u32(b_ptr(s))) + static_cast<uint32_t>(h) * ((C::LOAD_N / 2) * 128 >> 4);
+                if (elect_one()) {
+#pragma unroll
+                  for (int k4 = 0; k4 < BLOCK_K / UMMA_K; ++k4)
+                    umma_f16<CG>(d_tmem, a_desc + 2 * k4, b_desc + 2 * k4, idesc_half, (kb | k4) != 0 ? 1u : 0u);
+                  if (h == 1) umma_commit<CG>(&empty[s]);
+                  if (kb == p.kblocks - 1) umma_commit<CG>(&tfull[as * 2 + h]);
+                }
+                __syncwarp();
+                if (++s == C::STAGES) { s = 0; ph ^= 1; }
+              }
+            }
+            continue;
+          }
           mbar_wait(&tempty[as], aph ^ 1);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * BLOCK_N;
@@ -312,10 +349,12 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       // do not tear the barriers down while the last remote arrivals may still be in flight
       if (iter > 0) {
         const uint32_t last = iter - 1;
-        mbar_wait(&tempty[last & 1], (last >> 1) & 1);
+        if (SPLIT) { mbar_wait(&tempty[(last & 1) * 2], (last >> 1) & 1); mbar_wait(&tempty[(last & 1) * 2 + 1], (last >> 1) & 1); }
+        else mbar_wait(&tempty[last & 1], (last >> 1) & 1);
         if (iter > 1) {
           const uint32_t prev = iter - 2;
-          mbar_wait(&tempty[prev & 1], (prev >> 1) & 1);
+          if (SPLIT) { mbar_wait(&tempty[(prev & 1) * 2], (prev >> 1) & 1); mbar_wait(&tempty[(prev & 1) * 2 + 1], (prev >> 1) & 1); }
+          else mbar_wait(&tempty[prev & 1], (prev >> 1) & 1);
         }
       }
     }
@@ -358,22 +397,35 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const uint32_t my_first = static_cast<uint32_t>((warp_buf0 - p.sink.cand) + static_cast<int64_t>(lane) * cap);
         const int64_t qrow = slot_qrow0(slot) + lane;
         const bool valid = qrow < p.nq;
-        float tau_next = valid ? tau_load(p.sink.tau_g, qrow) : cur.tau;
+        uint32_t tau_next_key = valid ? tau_load_key(p.sink.tau_g, qrow) : 0u;   // raw key: converted where it is used (sink.cuh)
 
         for (int64_t t = r0 + lo; t < r0 + hi; ++t, ++iter) {
           if (SETS == 2 && (iter & 1u) != set) continue;  // the other set's accumulator buffer
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
-          mbar_wait(&tfull[as], aph);
+          // SPLIT: barrier pair of this buffer's halves; the second half is waited for just before its first load
+          uint64_t* const tf = SPLIT ? &tfull[as * 2] : &tfull[as];
+          uint64_t* const te = SPLIT ? &tempty[as * 2] : &tempty[as];
+          mbar_wait(tf, aph);
           tc_fence_after();
           const int32_t col0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_N);
+          // corpus row (within the tile) of the first column of 32-column slice ch -- see SPLIT above the kernel
+          auto slice_row = [&](int ch) -> int32_t {
+            if (!SPLIT || CG == 1) return ch * 32;
+            const int h = ch >> 2, j = ch & 3;
+            return (j < 2) ? 64 * h + 32 * j : 128 + 64 * h + 32 * (j - 2);
+          };
+          auto hand_back = [&](uint64_t* bar) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(bar, 0); else mbar_arrive(bar); }
+          };
           // slow-path epilogue: the last corpus tile (rows past n are TMA zero fill) or the L2 metric
           const bool adj = (col0 + BLOCK_N > n_rows) || (p.half_norm != nullptr);
           const uint32_t tbase = taddr + as * BLOCK_N;
           if (NXF_K1_DBG(p.debug, 2)) {
             // pipeline timing only: hand the accumulator back without reading it
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]); }
+            hand_back(te);
+            if (SPLIT) { mbar_wait(tf + 1, aph); tc_fence_after(); hand_back(te + 1); }
             continue;
           }
           // Phase A (holds the accumulator): two register buffers, the tcgen05.ld of slice ch+1 is in flight while slice
@@ -385,27 +437,31 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             tmem_ld_wait_dep(va);
             tmem_ld32(tbase + (ch + 1) * 32, vb);
             if (!NXF_K1_DBG(p.debug, 1)) {
-              if (adj) epi_chunk<true>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
-              else epi_chunk<false>(va, col0 + ch * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+              if (adj) epi_chunk<true>(va, col0 + slice_row(ch), n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+              else epi_chunk<false>(va, col0 + slice_row(ch), n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
             }
             tmem_ld_wait_dep(vb);
+            if (SPLIT && ch + 2 == BLOCK_N / 64) {
+              // first half fully read: back to the issuer (which starts the next tile's first half at once); second half ready?
+              hand_back(te);
+              mbar_wait(tf + 1, aph);
+              tc_fence_after();
+            }
             if (ch + 2 < BLOCK_N / 32) {
               tmem_ld32(tbase + (ch + 2) * 32, va);
             } else {
-              // accumulator fully read: hand the TMEM buffer back to the MMA issuer
-              tc_fence_before();
-              __syncwarp();
-              if (lane == 0) { if (CG == 2 && rank != 0) mbar_arrive_cluster(&tempty[as], 0); else mbar_arrive(&tempty[as]); }
+              // accumulator fully read: hand the TMEM buffer (SPLIT: its second half) back to the MMA issuer
+              hand_back(SPLIT ? te + 1 : te);
             }
             if (!NXF_K1_DBG(p.debug, 1)) {
-              if (adj) epi_chunk<true>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
-              else epi_chunk<false>(vb, col0 + (ch + 1) * 32, n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+              if (adj) epi_chunk<true>(vb, col0 + slice_row(ch + 1), n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+              else epi_chunk<false>(vb, col0 + slice_row(ch + 1), n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
             }
           }
           NXF_DEV_CHECK(cur.cnt <= cap, "K1 private candidate buffer overflow");
           // other owners' progress on this query: loaded during the previous tile, folded in only now so that its latency
           // hides behind phase A
-          cur.tau = fmaxf(cur.tau, tau_next);
+          cur.tau = fmaxf(cur.tau, tau_from_key(tau_next_key));
           // Phase B (the accumulator is already back with the MMA issuer): rows whose buffer could overflow during the next
           // tile (<= 256 appends) are reduced to their exact top-k' by the whole warp; tau rises to the k'-th score and is
           // published for the other owners of the query
@@ -436,7 +492,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             atomicAdd(reinterpret_cast<unsigned long long*>(p.prof), static_cast<unsigned long long>(pn));
             atomicAdd(reinterpret_cast<unsigned long long*>(p.prof) + 1, static_cast<unsigned long long>(clock64() - pc0));
           }
-          if (valid) tau_next = tau_load(p.sink.tau_g, qrow);
+          if (valid) tau_next_key = tau_load_key(p.sink.tau_g, qrow);
         }
       }
     }
@@ -537,10 +593,10 @@ static int encode_tmap_2d_sw128(CUtensorMap* m, const void* base, int64_t rows, 
   return NXF_OK;
 }
 
-template <int CG, bool BF16, int SETS>
+template <int CG, bool BF16, int SETS, bool SPLIT = false>
 static int launch_k1_t(const CUtensorMap& tq, const CUtensorMap& tc, const CUtensorMap& tc2, const K1Params& p, int grid, cudaStream_t stream) {
   using C = k1::Cfg<CG>;
-  auto kern = k1_search_kernel<CG, BF16, SETS>;
+  auto kern = k1_search_kernel<CG, BF16, SETS, SPLIT>;
   if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), C::SMEM_BYTES)) return rc;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(static_cast<unsigned>(grid));
@@ -574,6 +630,11 @@ int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, 
     if (rc) return rc;
   } else {
     tc2 = tc;
+  }
+  if (p.split) {
+    if (p.epi_sets != 2 || p.kblocks > 2) { set_error("k1: split accumulators need two epilogue sets and <= 2 K blocks per tile"); return NXF_EINVAL; }
+    if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 2, true>(tq, tc, tc2, p, grid, stream) : launch_k1_t<2, false, 2, true>(tq, tc, tc2, p, grid, stream);
+    return bf16 ? launch_k1_t<1, true, 2, true>(tq, tc, tc2, p, grid, stream) : launch_k1_t<1, false, 2, true>(tq, tc, tc2, p, grid, stream);
   }
   if (p.epi_sets == 2) {
     if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 2>(tq, tc, tc2, p, grid, stream) : launch_k1_t<2, false, 2>(tq, tc, tc2, p, grid, stream);

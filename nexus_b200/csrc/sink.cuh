@@ -36,9 +36,15 @@ __device__ __forceinline__ void warp_flush(const SinkParams& sp, const Entry* __
   for (int i = lane_id(); i < n; i += 32) dst[i] = buf[i];
 }
 
+__device__ __forceinline__ float tau_from_key(uint32_t key) { return key <= kKeyNegInf ? -INFINITY : okey_inv(key); }
 __device__ __forceinline__ float tau_load(const uint32_t* tau_g, int64_t query) {
-  uint32_t key = *reinterpret_cast<const volatile uint32_t*>(tau_g + query);
-  return key <= kKeyNegInf ? -INFINITY : okey_inv(key);
+  return tau_from_key(*reinterpret_cast<const volatile uint32_t*>(tau_g + query));
+}
+// The load alone: a warp stalls at the first instruction that USES a loaded register, and tau_load's key -> float conversion is
+// that instruction -- a prefetched threshold must stay a raw key until the point of use (K1 on 64-d rows spent 5.5 % of its stall
+// samples on the conversion, i.e. on an L2 round trip per tile that the tile's own work was meant to hide).
+__device__ __forceinline__ uint32_t tau_load_key(const uint32_t* tau_g, int64_t query) {
+  return *reinterpret_cast<const volatile uint32_t*>(tau_g + query);
 }
 
 }  // namespace nxf
