@@ -942,17 +942,11 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
       if (kp.fold) kp.nq_pad = (kp.nq_pad + 31) & ~31;   // 32-column accumulator loads (P.nq_t was planned the same way)
       kp.q_f32 = q_f32; kp.ldq = idx->ld; kp.dim = idx->dim; kp.max_norm2 = idx->max_norm2;
       kp.stages = k2t_plan_stages(kp.kblocks, kp.nq_pad, kp.fold);
-      // (an even number of sets: a set then only ever sees tiles of one issuer, which complete in order -- its parity wait on an
-      // accumulator buffer would otherwise be able to run a whole phase ahead of the other issuer)
-      kp.issuers = (kp.stages >= 2 * kp.kblocks && P.epi_sets % 2 == 0 && env_int("NXF_K2T_ISSUERS", 1) == 2) ? 2 : 1;
       kp.tbuf_stride = kp.nq_pad <= 32 ? 32 : (kp.nq_pad <= 64 ? 64 : 128);
       kp.tbufs = std::min(8, 512 / kp.tbuf_stride);
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.check_every = P.rw;
       kp.epi_sets = P.epi_sets;
-      // NXF_K2T_CS=2 (experiment, no gain measured: 297.7 vs 297.7 us at 128 queries): pairs of sets share a tile, half the slices each
-      kp.col_split = (P.epi_sets % 2 == 0 && kp.nq_pad >= 32 && env_int("NXF_K2T_CS", 1) == 2) ? 2 : 1;
-      if (kp.fold) kp.col_split = 1;   // the folded filter takes whole rows
       kp.sink = sink;
       kp.sink.cap = P.cap;
       const int64_t c_ld = idx->ld;

@@ -108,8 +108,6 @@ struct K2TParams {
   int tbuf_stride;  // TMEM columns between buffers
   int check_every;  // tiles per epilogue set between two buffer-overflow checks (cap = 2k' + epi_sets*128*check_every)
   int epi_sets;     // 2..4 epilogue warp sets (four warps each, one per SM sub-partition); set s filters tiles s, s + epi_sets, ...
-  int issuers;      // 1, or 2 (stages >= 2 * kblocks): two warps issue the MMAs of alternate tiles
-  int col_split;    // 1, or 2 (epi_sets even): pairs of sets share a tile, each filtering half of the query slices
   // a search is 1-3 launches over consecutive tile ranges (DESIGN.md "K2T, threshold seeding"); the per-(CTA, query) lists and
   // their counts stay in global memory between launches
   int64_t tile_begin, tile_end;  // this launch streams (virtual) corpus tiles [tile_begin, tile_end), CTA b takes tile_begin + b + i * grid

@@ -24,6 +24,11 @@ namespace nxf {
 #ifndef NXF_K2T_KNOCKOUT
 #define NXF_K2T_KNOCKOUT 0
 #endif
+// who issues inside the producer warp: 1 = the lane elect.sync picks, 0 = lane 0 (same-box A/B with tools/build_variant.sh: no
+// difference; the issuer warp's choice follows the template parameter SETS, see the issuer)
+#ifndef NXF_K2T_ELECT_PRODUCER
+#define NXF_K2T_ELECT_PRODUCER 1
+#endif
 
 namespace k2t {
 constexpr int BLOCK_M = 128;   // corpus rows per tile
@@ -208,7 +213,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int b = 0; b < p.tbufs; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4 * p.col_split); }
+    for (int b = 0; b < p.tbufs; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
     mbar_init(qfull, 1);
     fence_mbar_init();
   }
@@ -272,7 +277,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       const int32_t row0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_M);
       for (int kb = 0; kb < p.kblocks; ++kb) {
         mbar_wait(&empty[s], ph ^ 1);
-        if (elect_one()) {
+        if (NXF_K2T_ELECT_PRODUCER ? elect_one() : lane == 0) {
           mbar_expect_tx(&full[s], A_BYTES);
           tma_load_2d(&tmap_c, &full[s], ring + s * A_BYTES, kb * BLOCK_K, row0, kEvictFirst);
         }
@@ -280,40 +285,40 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
     }
     __syncwarp();
-  } else if (warp == 1 || (warp == 3 && p.issuers == 2)) {
-    // ============================== MMA issuers ==============================
+  } else if (warp == 1) {
+    // ============================== MMA issuer ==============================
     // The issuing thread paces the whole stream on short rows (one K block per tile: a tile every ~700 clocks at HBM speed), so the
     // per-tile instruction chain is kept short: running counters instead of divisions, descriptors advanced by addition, warp-uniform
-    // loop.  It is still ~120 dependent instructions per tile (two barrier waits, the elect loops nvcc wraps around every
-    // tcgen05 instruction, the uniform-datapath address arithmetic): ~800 clocks with sixteen epilogue warps competing for the issue
-    // slots, i.e. the tile period the profile of the one-issuer kernel showed at 128 queries (profiles/r2_k2t_issuer.md).  Two
-    // warps therefore issue alternate tiles (the tiles are independent: own accumulator buffer, own ring stages, own commits).
-    // Only with stages >= 2 * kblocks (K2TParams::issuers, set by the host): a parity wait is only meaningful one phase ahead of the
-    // barrier, and the second issuer's first wait is on ring position kblocks .. 2 * kblocks - 1 while nothing has been loaded yet.
-    const uint32_t me = warp == 1 ? 0u : 1u;
-    const uint32_t n_iss = static_cast<uint32_t>(p.issuers);
+    // loop.  (A second issuer warp on alternate tiles and pairs of warp sets sharing a tile were built and measured in round 2 --
+    // no gain at 128 queries, and their run-time parameters in these loops cost the 1-32 query kernels 3-5 %: removed again,
+    // profiles/r2_k2t_knockout.md.)
     const uint32_t idesc = umma_idesc_f16(BF16, BLOCK_M, p.nq_pad);
     mbar_wait(qfull, 0);
     tc_fence_after();
-    // this issuer's first tile is tile `me` of the CTA: ring stage (me * kblocks) % stages, accumulator buffer me
     int s = 0;
     uint32_t ph = 0;
-    for (uint32_t i = 0; i < me * static_cast<uint32_t>(p.kblocks); ++i) if (++s == p.stages) { s = 0; ph ^= 1; }
-    uint32_t b = me, bph = 0;   // tbufs is even (4 or 8): the buffers alternate between the issuers as the tiles do
+    uint32_t b = 0, bph = 0;
     const uint64_t a_desc0 = umma_desc_sw128(smem_u32(ring));          // stage s: + s * (A_BYTES >> 4) in the address field
     const uint64_t b_desc0 = umma_desc_sw128(smem_u32(q_smem));        // query block qb: + qb * (nq_pad * 128 >> 4)
     const uint32_t q_blk = static_cast<uint32_t>(p.nq_pad) * 8u;
     const uint64_t ones_desc = umma_desc_sw128(smem_u32(ones_tile));
     const uint64_t tauq_desc0 = umma_desc_sw128(smem_u32(tauq_tile));  // version v: + v * (tq_bytes >> 4)
     const uint32_t fold_round = static_cast<uint32_t>(EPI_SETS) * static_cast<uint32_t>(p.check_every);
-    uint32_t in_round = me, fold_ver = 0;   // position of this issuer's tile in its round (fold_round >= 2)
-    for (int64_t t = t_first + static_cast<int64_t>(me) * gridDim.x; t < t_end; t += static_cast<int64_t>(n_iss) * gridDim.x) {
+    uint32_t in_round = 0, fold_ver = 0;
+    for (int64_t t = t_first; t < t_end; t += gridDim.x) {
       mbar_wait(&tempty[b], bph ^ 1);
       const uint32_t d_tmem = tmem_base + b * p.tbuf_stride;
       for (int kb = 0; kb < p.kblocks; ++kb) {
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        if (elect_one()) {
+        // Who issues: the lane elect.sync picks (kernels with three or four warp sets, i.e. more than 32 queries) or lane 0 (two
+        // sets).  Under `lane == 0` nvcc wraps each tcgen05 instruction in an elect-and-retry loop (five dependent instructions each);
+        // under elect.sync the MMAs and commits of a tile are consecutive.  Same box, C5 corpus, k = 10, whole search: 64 queries
+        // 0.272 -> 0.243 ms and 128 queries 0.342 -> 0.334 ms with elect.sync, but 1 / 8 queries 0.234 / 0.239 -> 0.243 / 0.245 ms
+        // (32: equal) -- hence both forms, chosen at compile time with the set count (a run-time choice between two copies in this
+        // loop cost the 32-query case 6 %; profiles/r2_k2t_elect_ab.log; the producer's TMA is insensitive to it).
+        constexpr bool ELECT_ISSUE = SETS >= 3;
+        auto issue_tile_step = [&]() {
           const uint64_t a_desc = a_desc0 + static_cast<uint32_t>(s) * static_cast<uint32_t>(A_BYTES >> 4);
           const uint64_t b_desc = b_desc0 + static_cast<uint32_t>(kb) * q_blk;
 #if NXF_K2T_KNOCKOUT != 3
@@ -326,21 +331,17 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             if (FOLD) umma_f16<1>(d_tmem, ones_desc, tauq_desc0 + fold_ver * static_cast<uint32_t>(tq_bytes >> 4), idesc, 1u);   // += -tau
             umma_commit<1>(&tfull[b]);
           }
+        };
+        if constexpr (ELECT_ISSUE) {
+          if (elect_one()) issue_tile_step();
+        } else {
+          if (lane == 0) issue_tile_step();
         }
         __syncwarp();
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
-      // two issuers: skip the other one's tile -- its ring stages, its accumulator buffer, its place in the round
-      if (n_iss == 2) {
-        s += p.kblocks;
-        while (s >= p.stages) { s -= p.stages; ph ^= 1; }
-      }
-      if (FOLD) {
-        in_round += n_iss;
-        while (in_round >= fold_round) { in_round -= fold_round; fold_ver ^= 1u; }
-      }
-      b += n_iss;
-      if (b >= static_cast<uint32_t>(p.tbufs)) { b -= static_cast<uint32_t>(p.tbufs); bph ^= 1; }
+      if (FOLD && ++in_round == fold_round) { in_round = 0; fold_ver ^= 1u; }
+      if (++b == static_cast<uint32_t>(p.tbufs)) { b = 0; bph ^= 1; }
     }
     __syncwarp();
   } else if (warp >= EPI_WARP0) {
@@ -350,13 +351,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // tiles at a named barrier, where the lists that could overflow are pruned while nobody appends.
     const int ew8 = warp - EPI_WARP0;  // 0..7
     const int ew = ew8 & 3;            // == warp % 4: the TMEM lane quarter this warp may read
-    // col_split == 2 (K2TParams): two warp groups share a tile, each filtering half of its query slices, so a tile occupies its
-    // accumulator buffer half as long and only EPI_SETS / 2 buffers are being read at any time -- with 128 queries there are four
-    // buffers in all, and four sets reading four tiles left the issuer no buffer to compute ahead into: every set then idled for a
-    // release -> MMA -> commit round trip per tile (a quarter of the epilogue's time in the profile).
-    const int tsets = EPI_SETS / p.col_split;     // groups of warps that take whole tiles in turn
-    const int set = (ew8 >> 2) / p.col_split;
-    const int half = (ew8 >> 2) % p.col_split;
+    const int set = ew8 >> 2;
     const int et = ew * 32 + static_cast<int>(lane);   // 0..127: corpus row within the tile
     const int eq = ew8 * 32 + static_cast<int>(lane);  // 0..255: the query this thread looks after (if < nq)
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
@@ -364,9 +359,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int k = p.sink.k;
     Entry* cta_cand = p.sink.cand + static_cast<int64_t>(blockIdx.x) * p.nq_pad * cap;  // [nq_pad][cap]
     uint32_t* cand_words = reinterpret_cast<uint32_t*>(cta_cand);
-    const int chunks_all = p.nq_pad / 16;
-    const int cpw = (chunks_all + p.col_split - 1) / p.col_split;
-    const int ch_begin = half * cpw, chunks = min(chunks_all, ch_begin + cpw);   // this warp's query slices [ch_begin, chunks)
+    const int chunks = p.nq_pad / 16;
     const uint32_t round_tiles = static_cast<uint32_t>(EPI_SETS) * static_cast<uint32_t>(p.check_every);  // tiles between two overflow checks / threshold refreshes
     // a list gains <= 128 entries per tile, i.e. <= 128 * round_tiles between two checks, and the counts read at a check are
     // exact (every appender has arrived at the barrier): cap - full_mark = one round of appends
@@ -381,7 +374,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     for (uint32_t r0 = 0; r0 < n_it; r0 += round_tiles, ver ^= 1u) {
       const uint32_t r1 = min(n_it, r0 + round_tiles);
       const float* tv = tauv + ver * MAX_NQ;
-      for (uint32_t iter = r0 + set; iter < r1; iter += tsets) {  // r0 is a multiple of EPI_SETS, hence of tsets: iter % tsets is the set
+      for (uint32_t iter = r0 + set; iter < r1; iter += EPI_SETS) {  // r0 is a multiple of EPI_SETS: iter % EPI_SETS is the set
         const int64_t t = t_first + static_cast<int64_t>(iter) * gridDim.x;
         const int64_t row = perm_tile(p.perm, t) * BLOCK_M + et;
         const bool row_ok = row < p.n;
@@ -465,9 +458,9 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         if (lane == 0) mbar_arrive(&tempty[b]);
         for (int ch = chunks; ch < chunks; ch += 2) {
 #else
-        tmem_ld16(tbase + ch_begin * 16, va);
+        tmem_ld16(tbase, va);
 #pragma unroll 1
-        for (int ch = ch_begin; ch < chunks; ch += 2) {
+        for (int ch = 0; ch < chunks; ch += 2) {
 #endif
           const TauSlice ta = k2t_load_tau(tau_s, ch);
           tmem_ld_wait_dep16(va);
@@ -498,7 +491,7 @@ k2t_stream_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           }
         }
         }  // !FOLD
-        b += static_cast<uint32_t>(tsets);
+        b += EPI_SETS;
         while (b >= static_cast<uint32_t>(p.tbufs)) { b -= static_cast<uint32_t>(p.tbufs); bph ^= 1u; }
       }
       if (p.no_check) continue;

@@ -1,7 +1,7 @@
-"""K2T's experimental modes (search_stream_tc.cu; off by default, behind NXF_K2T_FOLD / NXF_K2T_ISSUERS / NXF_K2T_CS) must give the
-same answers as the shipped path: the threshold folded into the MMA (whole-row filter on score - tau), two MMA issuer warps on
-alternate tiles, pairs of warp sets sharing a tile.  Short rows (one and two K blocks), query counts on both sides of the 64-column
-accumulator stride, a corpus large enough for the sampled-threshold launches, raw candidate pass and certified search."""
+"""K2T's experimental mode (search_stream_tc.cu; off by default, behind NXF_K2T_FOLD) must give the same answers as the shipped path:
+the threshold folded into the MMA (whole-row filter on score - tau), with each number of epilogue warp sets.  Short rows (one and two
+K blocks), query counts on both sides of the 64-column accumulator stride, a corpus large enough for the sampled-threshold launches,
+raw candidate pass and certified search."""
 import os
 
 import numpy as np
@@ -13,15 +13,14 @@ pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300, method="thread")]   # a 
 
 VARIANTS = {
     "fold": {"NXF_K2T_FOLD": "1"},
-    "two_issuers": {"NXF_K2T_ISSUERS": "2", "NXF_K2T_SETS": "4"},
-    "col_split": {"NXF_K2T_CS": "2", "NXF_K2T_SETS": "4"},
-    "fold_two_issuers": {"NXF_K2T_FOLD": "1", "NXF_K2T_ISSUERS": "2", "NXF_K2T_SETS": "2"},
+    "fold_sets2": {"NXF_K2T_FOLD": "1", "NXF_K2T_SETS": "2"},
+    "fold_sets4": {"NXF_K2T_FOLD": "1", "NXF_K2T_SETS": "4"},
 }
 
 
 @pytest.fixture
 def k2t_env(request):
-    saved = {k: os.environ.get(k) for k in ("NXF_K2T_FOLD", "NXF_K2T_ISSUERS", "NXF_K2T_CS", "NXF_K2T_SETS")}
+    saved = {k: os.environ.get(k) for k in ("NXF_K2T_FOLD", "NXF_K2T_SETS")}
     os.environ.update(VARIANTS[request.param])     # the library reads its switches with getenv at every call
     yield request.param
     for k, v in saved.items():

@@ -12,8 +12,6 @@ R=$(cd $(dirname $0)/.. && pwd)/nexus_b200
 run() { tag=$1; shift; echo "== $tag: $*" >> $L; env "$@" timeout -s KILL 100 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:k2t_stream -c 8 --csv python -u tools/sweep_small.py --config c5 --k $K --nqs $NQS --iters 2 2>&1 | grep -v "^==" | awk -F'","' '/k2t_stream/ {print $(NF)}' | sed 's/"//g' | tr '\n' ' ' >> $L; echo >> $L; }
 run shipped NXF_K2T_FOLD=0
 run fold NXF_K2T_FOLD=1
-run two_issuers NXF_K2T_ISSUERS=2
-run col_split NXF_K2T_CS=2
 for n in 2 1 3 5; do
   [ -f $R/libnexus_flat_k2t_ko$n.so ] && run ko$n NEXUS_FLAT_LIB=$R/libnexus_flat_k2t_ko$n.so
 done
