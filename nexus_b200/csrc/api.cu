@@ -1030,7 +1030,11 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
       kp.num_qt = static_cast<int>(ceil_div64(bn, 128 * P.cta_group));
       kp.epi_sets = P.epi_sets;
       // short rows: the accumulator in two halves, so that a set never waits for the whole MMA of its next tile
-      kp.split = (P.epi_sets == 2 && kp.kblocks <= 2 && env_int("NXF_K1_SPLIT", 1) != 0) ? 1 : 0;
+      // (NXF_K1_SPLIT=0: whole accumulators; =2: required -- the call fails if the plan does not allow it, so that a test knows it ran)
+      const int split_env = env_int("NXF_K1_SPLIT", 1);
+      kp.split = (P.epi_sets == 2 && kp.kblocks <= 2 && split_env != 0) ? 1 : 0;
+      NXF_REQUIRE(split_env != 2 || kp.split, "nxf_search: NXF_K1_SPLIT=2 but the plan has %d epilogue set(s) and %d K blocks per tile",
+                  P.epi_sets, kp.kblocks);
       kp.half_norm = l2 ? idx->half_norm : nullptr;
       kp.debug = env_int("NXF_K1_DEBUG", 0);
       kp.est_only = 0;
