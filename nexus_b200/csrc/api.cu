@@ -776,7 +776,10 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
       const int kb_tile = static_cast<int>(idx->ld / 64) * (P.seg_mode == 1 ? 3 : (P.seg_mode == 2 ? 2 : 1));
       // small searches (C1: 21 tile-units per cluster) lose 7 % to the second set's fixed costs (twice the lists to flush and merge)
       const int64_t units_per_cluster = static_cast<int64_t>(P.num_qt) * P.n_tiles / std::max(used, 1);
-      P.epi_sets = std::max(1, std::min(2, env_int("NXF_K1_SETS", (kb_tile <= 8 && units_per_cluster >= 128) ? 2 : 1)));
+      // rows of one or two K blocks: four groups on split accumulators (C5 full batch, same box: kernel 31.9 -> 27.8 ms; D = 128 40.0 -> 37.2 ms)
+      const int want = env_int("NXF_K1_SETS", units_per_cluster >= 128 ? (kb_tile <= 2 ? 4 : (kb_tile <= 8 ? 2 : 1)) : 1);
+      // four groups exist only with the split accumulators (rows of <= 2 K blocks, search_tc.cu)
+      P.epi_sets = (want >= 4 && kb_tile <= 2) ? 4 : (want >= 2 ? 2 : 1);
     }
     P.owners = static_cast<int64_t>(P.grid) * 128 * 2 * P.epi_sets;  // two query-tile slots per CTA, one buffer per (slot, set, row)
     // arena slice of a query: the list left by the sample passes (<= k' entries) + up to cap entries from every (cluster, set) that
@@ -1032,7 +1035,7 @@ static int search_locked(nxf_index* idx, const void* q, int64_t nq, int q_dtype,
       // short rows: the accumulator in two halves, so that a set never waits for the whole MMA of its next tile
       // (NXF_K1_SPLIT=0: whole accumulators; =2: required -- the call fails if the plan does not allow it, so that a test knows it ran)
       const int split_env = env_int("NXF_K1_SPLIT", 1);
-      kp.split = (P.epi_sets == 2 && kp.kblocks <= 2 && split_env != 0) ? 1 : 0;
+      kp.split = (P.epi_sets >= 2 && kp.kblocks <= 2 && (split_env != 0 || P.epi_sets == 4)) ? 1 : 0;
       NXF_REQUIRE(split_env != 2 || kp.split, "nxf_search: NXF_K1_SPLIT=2 but the plan has %d epilogue set(s) and %d K blocks per tile",
                   P.epi_sets, kp.kblocks);
       kp.half_norm = l2 ? idx->half_norm : nullptr;

@@ -362,7 +362,12 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   } else if (warp >= EPI_WARP0) {
     // ============================== epilogue ==============================
     const int ew = (warp - EPI_WARP0) & 3;  // == warp % 4: the TMEM lane quarter this warp may read
-    const uint32_t set = static_cast<uint32_t>(warp - EPI_WARP0) >> 2;  // 0 .. SETS-1
+    // grp = owner index of this warp's rows (its own thresholds, counters, candidate buffers).  SETS = 4 (SPLIT only): the two groups of
+    // a buffer take one 128-column half each -- group (set, half) waits for, reads and hands back exactly that half.
+    static_assert(SETS != 4 || SPLIT, "four groups need the split accumulators");
+    const uint32_t grp = static_cast<uint32_t>(warp - EPI_WARP0) >> 2;  // 0 .. SETS-1
+    const uint32_t set = SETS == 4 ? (grp & 1u) : grp;                   // the accumulator buffer (tile parity) it filters
+    const uint32_t my_half = SETS == 4 ? (grp >> 1) : 0u;
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
     const int cap = p.sink.cap;
     const int k = p.sink.k;
@@ -371,7 +376,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     // this cluster's (at most two) query tiles: slot 0 = qt_base, slot 1 = qt_base + 1
     const int64_t qt_base = cluster_id * p.num_qt / num_clusters;
     auto slot_buf0 = [&](int slot) {  // lane 0's candidate buffer of this warp for that slot
-      return p.sink.cand + (((static_cast<int64_t>(blockIdx.x) * 2 + slot) * SETS + set) * BLOCK_M + ew * 32) * cap;
+      return p.sink.cand + (((static_cast<int64_t>(blockIdx.x) * 2 + slot) * SETS + grp) * BLOCK_M + ew * 32) * cap;
     };
     auto slot_qrow0 = [&](int slot) { return ((qt_base + slot) * CG + rank) * BLOCK_M + ew * 32; };
     auto slot_valid = [&](int slot) { return qt_base + slot < p.num_qt && slot_qrow0(slot) + lane < p.nq; };
@@ -400,11 +405,11 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         uint32_t tau_next_key = valid ? tau_load_key(p.sink.tau_g, qrow) : 0u;   // raw key: converted where it is used (sink.cuh)
 
         for (int64_t t = r0 + lo; t < r0 + hi; ++t, ++iter) {
-          if (SETS == 2 && (iter & 1u) != set) continue;  // the other set's accumulator buffer
+          if (SETS >= 2 && (iter & 1u) != set) continue;  // the other set's accumulator buffer
           const uint32_t as = iter & 1, aph = (iter >> 1) & 1;
           // SPLIT: barrier pair of this buffer's halves; the second half is waited for just before its first load
-          uint64_t* const tf = SPLIT ? &tfull[as * 2] : &tfull[as];
-          uint64_t* const te = SPLIT ? &tempty[as * 2] : &tempty[as];
+          uint64_t* const tf = SPLIT ? &tfull[as * 2 + my_half] : &tfull[as];
+          uint64_t* const te = SPLIT ? &tempty[as * 2 + my_half] : &tempty[as];
           mbar_wait(tf, aph);
           tc_fence_after();
           const int32_t col0 = static_cast<int32_t>(perm_tile(p.perm, t) * BLOCK_N);
@@ -425,12 +430,25 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           if (NXF_K1_DBG(p.debug, 2)) {
             // pipeline timing only: hand the accumulator back without reading it
             hand_back(te);
-            if (SPLIT) { mbar_wait(tf + 1, aph); tc_fence_after(); hand_back(te + 1); }
+            if (SPLIT && SETS != 4) { mbar_wait(tf + 1, aph); tc_fence_after(); hand_back(te + 1); }
             continue;
           }
           // Phase A (holds the accumulator): two register buffers, the tcgen05.ld of slice ch+1 is in flight while slice
           // ch is filtered
-          uint32_t va[32], vb[32];
+          uint32_t va[32];
+          if constexpr (SETS == 4) {
+            // 640 threads: 102 registers each leave no room for two slices in flight; twenty resident warps hide the load instead
+            const int c0 = static_cast<int>(my_half) * (BLOCK_N / 64);
+#pragma unroll 1
+            for (int ch = c0; ch < c0 + BLOCK_N / 64; ++ch) {
+              tmem_ld32(tbase + ch * 32, va);
+              tmem_ld_wait_dep(va);
+              if (ch + 1 == c0 + BLOCK_N / 64) hand_back(te);
+              if (adj) epi_chunk<true>(va, col0 + slice_row(ch), n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+              else epi_chunk<false>(va, col0 + slice_row(ch), n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
+            }
+          } else {
+          uint32_t vb[32];
           tmem_ld32(tbase, va);
 #pragma unroll 1
           for (int ch = 0; ch < BLOCK_N / 32; ch += 2) {
@@ -458,6 +476,7 @@ k1_search_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
               else epi_chunk<false>(vb, col0 + slice_row(ch + 1), n_rows, p.half_norm, cur, cand_words, my_first, p.debug, p.est_only);
             }
           }
+          }  // SETS != 4
           NXF_DEV_CHECK(cur.cnt <= cap, "K1 private candidate buffer overflow");
           // other owners' progress on this query: loaded during the previous tile, folded in only now so that its latency
           // hides behind phase A
@@ -632,7 +651,11 @@ int launch_k1(int store_dtype, int cta_group, const void* q16, int64_t nq_rows, 
     tc2 = tc;
   }
   if (p.split) {
-    if (p.epi_sets != 2 || p.kblocks > 2) { set_error("k1: split accumulators need two epilogue sets and <= 2 K blocks per tile"); return NXF_EINVAL; }
+    if ((p.epi_sets != 2 && p.epi_sets != 4) || p.kblocks > 2) { set_error("k1: split accumulators need two or four epilogue sets and <= 2 K blocks per tile"); return NXF_EINVAL; }
+    if (p.epi_sets == 4) {
+      if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 4, true>(tq, tc, tc2, p, grid, stream) : launch_k1_t<2, false, 4, true>(tq, tc, tc2, p, grid, stream);
+      return bf16 ? launch_k1_t<1, true, 4, true>(tq, tc, tc2, p, grid, stream) : launch_k1_t<1, false, 4, true>(tq, tc, tc2, p, grid, stream);
+    }
     if (cta_group == 2) return bf16 ? launch_k1_t<2, true, 2, true>(tq, tc, tc2, p, grid, stream) : launch_k1_t<2, false, 2, true>(tq, tc, tc2, p, grid, stream);
     return bf16 ? launch_k1_t<1, true, 2, true>(tq, tc, tc2, p, grid, stream) : launch_k1_t<1, false, 2, true>(tq, tc, tc2, p, grid, stream);
   }

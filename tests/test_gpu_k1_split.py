@@ -1,6 +1,7 @@
 """K1's split accumulators (search_tc.cu, template SPLIT; rows of one or two K blocks with two epilogue warp sets): each 256-column
 accumulator is computed and handed over as two 128-column halves, and under cta_group::2 a half holds corpus rows of BOTH CTAs'
-slices, so the epilogue remaps slice -> corpus row.  The planner only takes two sets on large problems; NXF_K1_SETS=2 forces them here
+slices, so the epilogue remaps slice -> corpus row; with four groups (the default on large short-row problems) each group waits for,
+reads and hands back one half.  The planner only takes more than one set on large problems; NXF_K1_SETS forces them here
 so that small cases cover the remapping: both CTA groupings, both metrics, a ragged last corpus tile, raw candidate pass and
 certified search, fp16 and bf16 rows.  NXF_K1_SPLIT=2 makes the library fail the call if the split kernel cannot be used (so the
 test knows it ran); NXF_K1_SPLIT=0 is the control (same answers from whole accumulators)."""
@@ -16,10 +17,11 @@ pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300, method="thread")]
 
 @pytest.fixture
 def k1_env(request):
+    """request.param = "<sets>:<split>": NXF_K1_SETS (2 = two sets, each reading both halves of its buffer; 4 = four groups, one half
+    each) and NXF_K1_SPLIT (2 = required, 0 = whole accumulators)."""
     keys = ("NXF_K1_SETS", "NXF_K1_SPLIT")
     saved = {k: os.environ.get(k) for k in keys}
-    os.environ["NXF_K1_SETS"] = "2"
-    os.environ["NXF_K1_SPLIT"] = request.param
+    os.environ["NXF_K1_SETS"], os.environ["NXF_K1_SPLIT"] = request.param.split(":")
     yield request.param
     for k, v in saved.items():
         if v is None:
@@ -28,7 +30,7 @@ def k1_env(request):
             os.environ[k] = v
 
 
-@pytest.mark.parametrize("k1_env", ["2", "0"], indirect=True)
+@pytest.mark.parametrize("k1_env", ["4:2", "2:2", "2:0"], indirect=True)
 @pytest.mark.parametrize("path", ["tensor", "tensor_1cta", "tensor_raw"])
 @pytest.mark.parametrize("dim,store,metric", [(64, "bf16", "ip"), (128, "f16", "ip"), (100, "bf16", "l2"), (64, "bf16", "l2")])
 def test_k1_split_matches_oracle(k1_env, path, dim, store, metric):
@@ -46,7 +48,7 @@ def test_k1_split_matches_oracle(k1_env, path, dim, store, metric):
                   rtol=2e-4 if raw else 1e-5, atol=2e-5 if raw else 1e-6)
 
 
-@pytest.mark.parametrize("k1_env", ["2"], indirect=True)
+@pytest.mark.parametrize("k1_env", ["4:2", "2:2"], indirect=True)
 def test_k1_split_ids_cover_every_slice(k1_env):
     """One planted best row per 32-row slice of a tile: every slice's remapped row index is exercised by an exact id check."""
     dim, n = 64, 256 * 8
