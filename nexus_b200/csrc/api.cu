@@ -607,6 +607,11 @@ static int plan_search(const nxf_index* idx, int64_t nq, int q_dtype, int k, int
   else if (flags & NXF_SEARCH_FORCE_TSTREAM) path = NXF_PATH_TSTREAM;
   // small batches stream the corpus once through the tensor cores (K2T); round 2: also a single query on long rows (same GB/s as
   // K2 there, and a tenth of its arena to merge) and fp32 storage, which streams its 2-byte hi plane instead of the 4-byte rows
+  // ... except 65-128 queries on 128-byte rows of a large corpus: there K2T is bound by its per-tile filter (one tile = 16 KB of stream),
+  // and K1 with four epilogue groups on split accumulators is faster (C5 corpus, same box: 128 queries k = 10 0.332 -> 0.287 ms,
+  // k = 500 0.429 -> 0.334 ms; 96 queries 0.305 -> 0.284 / 0.391 -> 0.326; at 64 queries K2T wins, 0.243 vs 0.296)
+  else if (tens && idx->ld == 64 && nq > env_int("NXF_TSTREAM_SHORT_MAX_NQ", 64) && nq <= NXF_TSTREAM_MAX_NQ &&
+           idx->n >= env_int("NXF_TSTREAM_SHORT_MIN_ROWS", 2000000) && (store16 || hi_ok)) path = NXF_PATH_TENSOR;
   else if (store16 && nq <= NXF_TSTREAM_MAX_NQ && nq >= env_int("NXF_TSTREAM_MIN_NQ", 1)) path = NXF_PATH_TSTREAM;
   else if (hi_ok && nq <= NXF_TSTREAM_MAX_NQ && nq >= env_int("NXF_TSTREAM_MIN_NQ_F32", 1)) path = NXF_PATH_TSTREAM;
   else if (nq <= NXF_STREAM_MAX_NQ) path = NXF_PATH_STREAM;

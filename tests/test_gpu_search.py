@@ -132,6 +132,16 @@ def test_tensor_stream_kernel_seeded(store, case):
         assert st["kernel_launches"] >= 6    # 2 converts, seed pass, seed threshold, main pass, merge
 
 
+@pytest.mark.parametrize("store", ["bf16", "f32"])
+def test_short_rows_many_queries_go_to_k1(store):
+    """65-128 queries on 128-byte rows of a large corpus: K1 (four epilogue groups on split accumulators) instead of K2T, whose
+    per-tile filter paces the stream there; 64 queries stay on K2T."""
+    n, d, k = 2_100_000, 64, 10
+    c, x = gen_inputs(n, d, 128, seed=1234)
+    run_and_check(c, x, k, store=store, path="auto", rtol=1e-5, expect_path="tensor", min_recall=0.999)
+    run_and_check(c, x[:64], k, store=store, path="auto", rtol=1e-5, expect_path="tstream", min_recall=0.999)
+
+
 def test_tensor_stream_kernel_sampled_thresholds_fallback():
     """Adversarial corpus for K2T's sample (148 CTAs, 2344 tiles of 128 rows -> every 15th tile is a sample tile): all rows that
     matter lie in sample tiles, the sampled threshold is far too high, every query must go through the fall-back launch."""
