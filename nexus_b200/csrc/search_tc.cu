@@ -166,7 +166,8 @@ __device__ __forceinline__ RoundPiece round_piece(const K1Params& p, int64_t r0,
 // SETS = epilogue warp sets.  One set (four warps, one per SM sub-partition) filters a 256 x 256 tile in ~3 600 clocks, bound by
 // dependent-issue latency; the MMAs of a tile take 512 clocks per K block, so from 7 K blocks on (D >= 448) one set hides behind the
 // tensor pipe.  Shorter rows get a second set on the other TMEM buffer (set s filters the tiles with iter % 2 == s), with its own
-// per-row thresholds, counters and candidate buffers -- to the rest of the search it is one more owner of the query.
+// per-row thresholds, counters and candidate buffers -- to the rest of the search it is one more owner of the query.  Rows of one or
+// two K blocks get four groups on split accumulators (SETS = 4 with SPLIT, below): 640 threads, 96 registers each.
 // SPLIT (rows of one or two K blocks, two sets): each 256-column accumulator is computed and handed over as two 128-column halves
 // with their own full / empty barriers (two N = 128 MMAs per K step instead of one N = 256).  With one buffer per set, a set that
 // hands its buffer back then waits for the whole MMA of its next tile (19 % of the epilogue's samples on 64-d rows); with halves, the
